@@ -1,0 +1,45 @@
+// Library-level entry points: version, error string, device check.
+#include <stdarg.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace tdssf {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int num_sms() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      cached = 148;
+  }
+  return cached;
+}
+
+}  // namespace tdssf
+
+extern "C" int tdssf_version(void) { return TDSSF_VERSION; }
+
+extern "C" const char* tdssf_last_error(void) { return tdssf::g_err; }
+
+extern "C" int tdssf_check_device(void) {
+  int dev = 0, major = 0;
+  TDSSF_CUDA(cudaGetDevice(&dev));
+  TDSSF_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) {
+    tdssf::set_error("tdssf is built for sm_100a only; current device is sm_%d*", major * 10);
+    return TDSSF_EDEVICE;
+  }
+  return TDSSF_OK;
+}

@@ -1,0 +1,208 @@
+/*
+ * tdssf.h — C ABI of the B200-native (sm_100a) cross-modal fusion hot path of 3DSSF.
+ *
+ * This is the drop-in boundary.  The reference (CharlesChang012/3D-Semantic-Segmentation-Fusion)
+ * has no FFI layer of its own: its hot path is a set of Python functions built from ATen ops.
+ * Every entry point below names the reference interface it replaces (file:line relative to the
+ * reference tree).  The Python mirror of the reference modules (package `utils/` under
+ * `3d-semantic-segmentation-fusion_b200/`) binds these with ctypes — see INTEGRATION.md.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
+ *   - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default stream);
+ *   - nothing is allocated behind the caller's back: outputs and workspaces are caller-owned,
+ *     workspace sizes come from the matching `*_workspace_bytes()` call;
+ *   - return value 0 = OK, negative = TDSSF_E*; `tdssf_last_error()` gives a thread-local message;
+ *   - calls are asynchronous with respect to the host (stream-ordered) unless stated otherwise;
+ *   - inputs are never written.
+ */
+#ifndef TDSSF_H_
+#define TDSSF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TDSSF_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define TDSSF_API __attribute__((visibility("default")))
+#else
+#define TDSSF_API
+#endif
+
+#define TDSSF_OK 0
+#define TDSSF_EINVAL (-1)  /* bad argument (shape, alignment, NULL)            */
+#define TDSSF_ECUDA (-2)   /* a CUDA runtime call or a launch failed           */
+#define TDSSF_ENOSUP (-3)  /* configuration not supported by this build        */
+#define TDSSF_EDEVICE (-4) /* the current device is not sm_100 (no fallback)   */
+
+/* token / operand element types */
+#define TDSSF_F32 0
+#define TDSSF_F16 1
+#define TDSSF_BF16 2
+
+/* one 16-byte "camera assignment" record per LiDAR point:
+ *   patch[c]  flat patch index (y*grid_w+x, clamped) of the point in camera c, c < 6
+ *   mask      bit c set  <=>  the point is valid in camera c (depth>0, inside the image)
+ *   count     popcount(mask)
+ * This is the compact hand-off between tdssf_project and the gather / fused kernels. */
+typedef struct tdssf_rec {
+  uint16_t patch[6];
+  uint8_t mask;
+  uint8_t count;
+  uint16_t pad_;
+} tdssf_rec;
+
+#define TDSSF_MAX_CAMS 6
+
+TDSSF_API int tdssf_version(void);
+TDSSF_API const char* tdssf_last_error(void);
+/* 0 if the current CUDA device is compute capability 10.x, TDSSF_EDEVICE otherwise. */
+TDSSF_API int tdssf_check_device(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * a1+a2+a3  projection, mask, pixel rescale, patch index
+ * replaces  multi_camera_projector            utils/fusion_model.py:14-86
+ *           scale_pixel_coords                utils/fusion_model.py:89-127
+ *           patch index in FeatureFusionModel.forward   utils/fusion_model.py:172-180,188
+ *
+ * xyz        points of sweep b start at xyz + b*sweep_stride; point v at + v*point_stride (floats);
+ *            (x,y,z) are the first three floats.  point_stride==4 with a 16-byte aligned base takes
+ *            the float4 path.
+ * K          [B,NC,3,3] fp32 row-major          Rt  [B,NC,4,4] fp32 row-major (lidar -> camera)
+ * img_hw     [B,2] fp32 (H,W) of the ORIGINAL images
+ * Outputs (any may be NULL):
+ *   pix      [B,NC,V,2] fp32 (u,v) in original pixels, -1 where invalid   (reference layout)
+ *   depth    [B,NC,V]   fp32 camera z, -1 where invalid
+ *   valid    [B,NC,V]   u8   0/1
+ *   flat_idx [B,NC,V]   i32  clamped flat patch index (needs resize_h/w, patch)
+ *   rec      [B,V]      tdssf_rec (NC <= 6)
+ * resize_h, resize_w, patch: encoder attributes (utils/camera.py:24-34); ignored when flat_idx and
+ * rec are both NULL.
+ * fp32 evaluation order is the reference's CPU order: extrinsic rows with separately
+ * rounded mul/add, intrinsic rows as an FMA chain, IEEE division. */
+TDSSF_API int tdssf_project(const float* xyz, int64_t sweep_stride, int64_t point_stride,
+                  const float* K, const float* Rt, const float* img_hw,
+                  int B, int V, int NC,
+                  int resize_h, int resize_w, int patch,
+                  float* pix, float* depth, uint8_t* valid, int32_t* flat_idx, tdssf_rec* rec,
+                  void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a4+a5  per-camera patch-token gather and masked mean over cameras
+ * replaces  utils/fusion_model.py:184-201
+ * tokens  [B,NC,M,Ci]  fp32 / fp16 / bf16 (tok_dtype), row-major, 16-byte aligned, Ci % 8 == 0
+ * rec     [B,V]
+ * feat    [B,V,Ci] fp32.  fp16/bf16 tokens: the mean is rounded to the token dtype as the reference's
+ *         same-dtype arithmetic does, then widened (the reference's torch.cat promotes to fp32).
+ * Precondition: tokens are finite (the reference reads and multiplies by 0 for invalid cameras;
+ * this kernel skips the load — SURVEY F4). */
+TDSSF_API int tdssf_gather_mean(const void* tokens, int tok_dtype, const tdssf_rec* rec,
+                      int B, int V, int NC, int M, int Ci,
+                      float* feat, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a6  fusion MLP  448 -> 256 -> 64 -> 16  (concat [point feature | image feature] first)
+ * replaces  FeatureFusionModel.mlp + torch.cat   utils/fusion_model.py:144-150,203-204
+ * Weights are nn.Linear layout (out,in) row-major fp32: W1[256,448] b1[256] W2[64,256] b2[64]
+ * W3[16,64] b3[16].  Column order of W1's `in` axis: 64 point-feature columns, then 384 image.
+ */
+typedef struct tdssf_mlp_weights {
+  const float* W1; const float* b1;
+  const float* W2; const float* b2;
+  const float* W3; const float* b3;
+} tdssf_mlp_weights;
+
+/* fp32 CUDA-core path (1e-5 parity mode).  x_pt [N,64], x_img [N,384], logits [N,16].
+ * h1 [N,256] / h2 [N,64] (post-ReLU activations) are written when non-NULL (saved for backward). */
+TDSSF_API int tdssf_mlp_fwd_f32(const float* x_pt, const float* x_img, int64_t N,
+                      const tdssf_mlp_weights* w_host, float* h1, float* h2, float* logits,
+                      void* stream);
+
+/* fp32 backward: given dlogits [N,16] and saved x/h1/h2, accumulates (+=) dW*, db* (fp32, caller
+ * zeroes them) and writes dx_pt [N,64] (gradient to the PTv3 feature).  No gradient is
+ * produced for the image feature (the reference image branch runs under inference_mode).
+ * workspace: tdssf_mlp_bwd_workspace_bytes(N). */
+typedef struct tdssf_mlp_grads {
+  float* dW1; float* db1; float* dW2; float* db2; float* dW3; float* db3;
+} tdssf_mlp_grads;
+TDSSF_API size_t tdssf_mlp_bwd_workspace_bytes(int64_t N);
+TDSSF_API int tdssf_mlp_bwd_f32(const float* x_pt, const float* x_img, const float* h1, const float* h2,
+                      const float* dlogits, int64_t N, const tdssf_mlp_weights* w_host,
+                      const tdssf_mlp_grads* g_host, float* dx_pt,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* bf16 shadow of the weights in the tensor-core operand layout (prepared once per optimizer step).
+ * packed must hold tdssf_mlp_pack_bytes() bytes. */
+TDSSF_API size_t tdssf_mlp_pack_bytes(void);
+TDSSF_API int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w_host, void* packed, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a1..a6 fused inference: project -> gather -> masked mean -> concat -> MLP (tcgen05, bf16 operands,
+ * fp32 accumulate) -> logits, without materialising the 1 536 B/point image feature.
+ * replaces  FeatureFusionModel.forward up to voxel_scores   utils/fusion_model.py:152-204
+ * x_pt    [B*V,64] fp32 point features (PTv3 output)
+ * logits  [B*V,16] fp32
+ * rec_out optional [B,V] camera-assignment records (NULL to skip). */
+TDSSF_API int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t point_stride,
+                     const float* K, const float* Rt, const float* img_hw,
+                     int B, int V, int NC, int resize_h, int resize_w, int patch,
+                     const void* tokens, int tok_dtype, int M, int Ci,
+                     const float* x_pt, const void* packed_weights,
+                     float* logits, tdssf_rec* rec_out, void* stream);
+
+/* tensor-core MLP on pre-gathered features (used by training forward and as the unfused check).
+ * x_img may be fp32 [N,384].  h1_bf16 / h2_bf16 optional saved activations. */
+TDSSF_API int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N, const void* packed_weights,
+                     float* logits, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a7  devoxelize: nearest voxel per raw point, gather, and the backward scatter-add
+ * replaces  LiDARFeatureEncoder.devoxelize   utils/lidar.py:120-172
+ * pts [B,P,pts_stride] / vox [B,V,vox_stride] (xyz first).  idx [B,P] int64 = argmin_v |p-v|^2,
+ * first index wins ties.  All V rows take part, zero padding included. */
+TDSSF_API int tdssf_devox_nn(const float* pts, int64_t pts_stride, const float* vox, int64_t vox_stride,
+                   int B, int P, int V, int64_t* idx, void* stream);
+/* out[b,p,:] = scores[b,idx[b,p],:]   scores [B,V,C], out [B,P,C] */
+TDSSF_API int tdssf_devox_gather(const float* scores, const int64_t* idx, int B, int P, int V, int C,
+                       float* out, void* stream);
+/* dscores[b,idx[b,p],:] += dout[b,p,:]   (dscores zeroed by the caller) */
+TDSSF_API int tdssf_devox_scatter_add(const float* dout, const int64_t* idx, int B, int P, int V, int C,
+                            float* dscores, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a8+a9+a10  CE + Lovasz-Softmax loss, forward and backward in one call
+ * replaces  CELSLoss.forward            utils/losses.py:19-70
+ *           lovasz_softmax_flat         LovaszSoftmax/pytorch/lovasz_losses.py:171-199
+ *           lovasz_grad                 LovaszSoftmax/pytorch/lovasz_losses.py:18-30
+ * logits  [n_rows,16] fp32    labels [n_rows] int64 in 0..16    mask [n_rows] u8 or NULL
+ * class_w [16] fp32 (device)
+ * Outputs:
+ *   out_scalars (device) float[4] = {total, ce, lovasz, n_present}; double-precision partials inside
+ *   n_valid_host: number of rows that survive mask & (label != ignore) — written after an internal
+ *                 stream synchronisation (the reference's boolean indexing synchronises here too)
+ *   preds, gt  [>= n_rows] int64 — first n_valid entries are meaningful, original row order
+ *   dlogits    [n_rows,16] fp32 or NULL: d total / d logits (zeros on dropped rows)
+ * Sort order of the Lovasz errors: descending value, ties by ascending original index.
+ * workspace: tdssf_cels_workspace_bytes(n_rows). */
+TDSSF_API size_t tdssf_cels_workspace_bytes(int64_t n_rows);
+TDSSF_API int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, const uint8_t* mask,
+                       int64_t n_rows, const float* class_w, float lambda_lovasz, int ignore_index,
+                       float* out_scalars, int64_t* n_valid_host, int64_t* preds, int64_t* gt,
+                       float* dlogits, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a11  confusion matrix
+ * replaces  compute_confusion_matrix   utils/evaluation.py:35-42
+ * preds, labels [n] int64 in 1..C; cm [C*C] int64, rows = truth; ACCUMULATES into cm. */
+TDSSF_API int tdssf_confusion(const int64_t* preds, const int64_t* labels, int64_t n, int C, int64_t* cm,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TDSSF_H_ */
