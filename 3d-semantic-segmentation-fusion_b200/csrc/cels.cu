@@ -1,0 +1,527 @@
+// a8+a9+a10: CE + Lovasz-Softmax loss, forward and backward (utils/losses.py:19-70,
+// LovaszSoftmax/pytorch/lovasz_losses.py:18-30,171-199).
+//
+//   1. flag rows (mask & label != ignore), count per 256-row tile, scan tile counts      -> N
+//   2. compact + softmax + weighted CE + argmax; emit 16 class segments of sort keys |fg - p_c|
+//   3. per-class segmented LSD radix sort, descending value, stable (ties by ascending index, F14):
+//      4 passes of 8 bits over key' = 0x3F800000 - bits(err)   (err in [0,1] => key' in [0, 2^30))
+//   4. per class: integer prefix sums of the sorted foreground flags -> Jaccard gradient -> dot
+//   5. closed-form backward through |.|, the sort permutation, softmax and CE -> dlogits
+// Everything is HBM-bound integer / fp32 work; there is no tensor-core stage.
+#include <algorithm>
+#include "common.cuh"
+
+namespace tdssf {
+
+constexpr int kC = 16;             // classes
+constexpr int kRowTile = 256;      // rows per CTA in the flag/compact kernels
+constexpr int kSortThreads = 256;
+constexpr int kKeysPerThread = 8;
+constexpr int kSortTile = kSortThreads * kKeysPerThread;  // 2048 keys per CTA
+constexpr int kRadixBits = 8, kBins = 1 << kRadixBits, kPasses = 4;
+constexpr uint32_t kOneBits = 0x3F800000u;
+
+struct CelsWs {
+  int* tile_count;      // [n_tiles_rows]
+  int* tile_offset;     // [n_tiles_rows]
+  int* n_valid;         // [1]
+  int* class_count;     // [16]  foreground count per class (G_c)
+  double* acc;          // [0]=sum w*nll  [1]=sum w  [2..17]=lovasz loss per class
+  int* rows;            // [N]   original row of compact row i
+  uint8_t* ylab;        // [N]   label-1
+  float* probs;         // [N,16]
+  float* dprob;         // [N,16] d lovasz_c / d p_c  (unscaled)
+  uint32_t* keys[2];    // [16*N]
+  uint32_t* vals[2];    // [16*N]
+  uint32_t* hist;       // [16][kBins][sort_tiles]
+  int* tile_fg;         // [16][sort_tiles]
+};
+
+static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static size_t carve(CelsWs* ws, char* base, int64_t n_rows) {
+  const int64_t row_tiles = ceil_div(n_rows, kRowTile);
+  const int64_t sort_tiles = ceil_div(n_rows, kSortTile);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  char* p;
+  p = take(row_tiles * sizeof(int)); if (ws) ws->tile_count = (int*)p;
+  p = take(row_tiles * sizeof(int)); if (ws) ws->tile_offset = (int*)p;
+  p = take(sizeof(int)); if (ws) ws->n_valid = (int*)p;
+  p = take(kC * sizeof(int)); if (ws) ws->class_count = (int*)p;
+  p = take(18 * sizeof(double)); if (ws) ws->acc = (double*)p;
+  p = take(n_rows * sizeof(int)); if (ws) ws->rows = (int*)p;
+  p = take(n_rows); if (ws) ws->ylab = (uint8_t*)p;
+  p = take(n_rows * kC * sizeof(float)); if (ws) ws->probs = (float*)p;
+  p = take(n_rows * kC * sizeof(float)); if (ws) ws->dprob = (float*)p;
+  for (int i = 0; i < 2; ++i) {
+    p = take(n_rows * kC * sizeof(uint32_t)); if (ws) ws->keys[i] = (uint32_t*)p;
+    p = take(n_rows * kC * sizeof(uint32_t)); if (ws) ws->vals[i] = (uint32_t*)p;
+  }
+  p = take((size_t)kC * kBins * sort_tiles * sizeof(uint32_t)); if (ws) ws->hist = (uint32_t*)p;
+  p = take((size_t)kC * sort_tiles * sizeof(int)); if (ws) ws->tile_fg = (int*)p;
+  return off + 256;
+}
+
+// ---- block-wide helpers (256 threads) -----------------------------------------------------------
+__device__ __forceinline__ int warp_incl_scan(int v) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  return v;
+}
+// exclusive scan of one int per thread over a 256-thread block; *total = block sum
+__device__ __forceinline__ int block_excl_scan256(int v, int* s_warp /*[9]*/, int* total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int incl = warp_incl_scan(v);
+  if (lane == 31) s_warp[w] = incl;
+  __syncthreads();
+  if (w == 0) {
+    int x = lane < 8 ? s_warp[lane] : 0;
+    int xi = warp_incl_scan(x);
+    if (lane < 8) s_warp[lane] = xi - x;
+    if (lane == 7) s_warp[8] = xi;
+  }
+  __syncthreads();
+  const int r = s_warp[w] + incl - v;
+  *total = s_warp[8];
+  __syncthreads();
+  return r;
+}
+
+__device__ __forceinline__ bool row_is_valid(const int64_t* labels, const uint8_t* mask, int64_t r, int ignore) {
+  if (mask && !mask[r]) return false;
+  return labels[r] != (int64_t)ignore;
+}
+
+// ---- 1. flags ----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRowTile)
+cels_count_kernel(const int64_t* __restrict__ labels, const uint8_t* __restrict__ mask, int64_t n_rows,
+                  int ignore, int* __restrict__ tile_count) {
+  const int64_t r = (int64_t)blockIdx.x * kRowTile + threadIdx.x;
+  const int f = (r < n_rows) && row_is_valid(labels, mask, r, ignore);
+  const int c = __syncthreads_count(f);
+  if (threadIdx.x == 0) tile_count[blockIdx.x] = c;
+}
+
+// single CTA: exclusive scan of `n` ints (n up to millions: chunked), total -> *out_total
+__global__ void __launch_bounds__(256)
+scan_ints_kernel(const int* __restrict__ in, int* __restrict__ out, int64_t n, int* __restrict__ out_total) {
+  __shared__ int s_warp[9];
+  int carry = 0;
+  for (int64_t base = 0; base < n; base += 256) {
+    const int64_t i = base + threadIdx.x;
+    const int v = i < n ? in[i] : 0;
+    int tot;
+    const int e = block_excl_scan256(v, s_warp, &tot);
+    if (i < n) out[i] = carry + e;
+    carry += tot;
+  }
+  if (threadIdx.x == 0 && out_total) *out_total = carry;
+}
+
+// ---- 2. compact + softmax + CE + keys ------------------------------------------------------------
+__global__ void __launch_bounds__(kRowTile)
+cels_compact_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels,
+                    const uint8_t* __restrict__ mask, int64_t n_rows, int ignore,
+                    const float* __restrict__ class_w, CelsWs ws, int64_t* __restrict__ preds,
+                    int64_t* __restrict__ gt) {
+  __shared__ int s_warp[9];
+  __shared__ int s_cls[kC];
+  __shared__ double s_red[2][8];
+  if (threadIdx.x < kC) s_cls[threadIdx.x] = 0;
+  const int64_t r = (int64_t)blockIdx.x * kRowTile + threadIdx.x;
+  const int f = (r < n_rows) && row_is_valid(labels, mask, r, ignore);
+  int tot;
+  const int local = block_excl_scan256(f, s_warp, &tot);  // also orders the s_cls init
+  const int N = *ws.n_valid;
+  double wnll = 0.0, wsum = 0.0;
+  if (f) {
+    const int i = ws.tile_offset[blockIdx.x] + local;
+    float x[kC];
+    const float4* src = reinterpret_cast<const float4*>(logits + r * kC);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float4 v = __ldg(src + q);
+      x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
+    }
+    const int y = (int)labels[r] - 1;  // 0..15 (ignore_index rows were dropped)
+    float m = x[0];
+#pragma unroll
+    for (int c = 1; c < kC; ++c) m = fmaxf(m, x[c]);
+    float e[kC], s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kC; ++c) { e[c] = expf(x[c] - m); s += e[c]; }
+    float p[kC];
+    int am = 0;
+    float pm = -1.f;
+#pragma unroll
+    for (int c = 0; c < kC; ++c) {
+      p[c] = __fdiv_rn(e[c], s);
+      if (p[c] > pm) { pm = p[c]; am = c; }  // first maximum wins, like torch.argmax
+    }
+    float xy = x[0];
+#pragma unroll
+    for (int c = 1; c < kC; ++c) xy = (c == y) ? x[c] : xy;
+    const bool y_ok = (y >= 0 && y < kC);
+    const float w = y_ok ? __ldg(class_w + y) : 0.f;
+    const float nll = logf(s) - (xy - m);
+    wnll = (double)w * (double)nll;
+    wsum = (double)w;
+    preds[i] = am + 1;
+    gt[i] = y + 1;
+    ws.rows[i] = (int)r;
+    ws.ylab[i] = (uint8_t)y;
+    float4* pd = reinterpret_cast<float4*>(ws.probs + (int64_t)i * kC);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) pd[q] = make_float4(p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
+#pragma unroll
+    for (int c = 0; c < kC; ++c) {
+      const float err = fabsf((c == y ? 1.f : 0.f) - p[c]);
+      ws.keys[0][(int64_t)c * N + i] = kOneBits - min(__float_as_uint(err), kOneBits);
+      ws.vals[0][(int64_t)c * N + i] = (uint32_t)i;
+    }
+    if (y_ok) atomicAdd(&s_cls[y], 1);
+  }
+  // block reduction of the CE partial sums
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    wnll += __shfl_xor_sync(0xffffffffu, wnll, o);
+    wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+  }
+  if (lane == 0) { s_red[0][wid] = wnll; s_red[1][wid] = wsum; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0, b = 0;
+    for (int i = 0; i < 8; ++i) { a += s_red[0][i]; b += s_red[1][i]; }
+    if (b != 0.0 || a != 0.0) { atomicAdd(ws.acc + 0, a); atomicAdd(ws.acc + 1, b); }
+  }
+  if (threadIdx.x < kC && s_cls[threadIdx.x]) atomicAdd(ws.class_count + threadIdx.x, s_cls[threadIdx.x]);
+}
+
+// ---- 3. segmented LSD radix sort ------------------------------------------------------------------
+// grid = (sort_tiles, 16 segments).  hist layout [seg][bin][tile] so that one exclusive scan per
+// segment yields the global offset of every (bin, tile) pair.
+__global__ void __launch_bounds__(kSortThreads)
+sort_hist_kernel(const uint32_t* __restrict__ keys, int N, int shift, int tiles,
+                 const int* __restrict__ class_count, uint32_t* __restrict__ hist) {
+  const int seg = blockIdx.y, tile = blockIdx.x;
+  if (class_count[seg] == 0) return;  // absent class: skipped by classes='present'
+  __shared__ uint32_t s_h[kBins];
+  s_h[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t* k = keys + (int64_t)seg * N;
+  const int base = tile * kSortTile;
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = base + j * kSortThreads + threadIdx.x;
+    if (idx < N) atomicAdd(&s_h[(k[idx] >> shift) & (kBins - 1)], 1u);
+  }
+  __syncthreads();
+  hist[((int64_t)seg * kBins + threadIdx.x) * tiles + tile] = s_h[threadIdx.x];
+}
+
+// one CTA per segment: in-place exclusive scan over kBins*tiles counters, 8 per thread per step
+__global__ void __launch_bounds__(256)
+sort_scan_kernel(uint32_t* __restrict__ hist, int tiles, const int* __restrict__ class_count) {
+  const int seg = blockIdx.x;
+  if (class_count[seg] == 0) return;
+  __shared__ int s_warp[9];
+  uint32_t* h = hist + (int64_t)seg * kBins * tiles;
+  const int64_t n = (int64_t)kBins * tiles;
+  int carry = 0;
+  for (int64_t base = 0; base < n; base += 2048) {
+    const int64_t i0 = base + threadIdx.x * 8;
+    uint32_t v[8];
+    int sum = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { v[j] = (i0 + j < n) ? h[i0 + j] : 0u; sum += (int)v[j]; }
+    int tot;
+    int run = carry + block_excl_scan256(sum, s_warp, &tot);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (i0 + j < n) h[i0 + j] = (uint32_t)run;
+      run += (int)v[j];
+    }
+    carry += tot;
+  }
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int N, int shift,
+                    int tiles, const int* __restrict__ class_count, const uint32_t* __restrict__ hist) {
+  const int seg = blockIdx.y, tile = blockIdx.x;
+  if (class_count[seg] == 0) return;
+  constexpr int kWarps = kSortThreads / 32;
+  __shared__ uint32_t s_cnt[kWarps][kBins];   // per-warp digit counters, then exclusive prefix over warps
+  __shared__ uint32_t s_base[kBins];          // global offset of (bin, tile)
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < kWarps * kBins; i += kSortThreads) (&s_cnt[0][0])[i] = 0;
+  s_base[threadIdx.x] = hist[((int64_t)seg * kBins + threadIdx.x) * tiles + tile];
+  __syncthreads();
+
+  const int64_t so = (int64_t)seg * N;
+  // warp w owns 256 consecutive keys of the tile, processed as 8 rounds of 32 consecutive keys so
+  // that (round, lane) order == key order  => the ranking below is stable
+  const int wbase = tile * kSortTile + w * (32 * kKeysPerThread);
+  uint32_t key[kKeysPerThread], val[kKeysPerThread], rank[kKeysPerThread];
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = wbase + j * 32 + lane;
+    const bool in = idx < N;
+    key[j] = in ? keys_in[so + idx] : 0xffffffffu;
+    val[j] = in ? vals_in[so + idx] : 0u;
+    const uint32_t d = (key[j] >> shift) & (kBins - 1);
+    const uint32_t act = __ballot_sync(0xffffffffu, in);
+    uint32_t r = 0;
+    if (in) {
+      const uint32_t peers = __match_any_sync(act, d);
+      const int leader = __ffs(peers) - 1;
+      uint32_t old = 0;
+      if (lane == leader) { old = s_cnt[w][d]; s_cnt[w][d] = old + __popc(peers); }
+      old = __shfl_sync(peers, old, leader);
+      r = old + __popc(peers & ((1u << lane) - 1));
+    }
+    rank[j] = r;
+    __syncwarp();
+  }
+  __syncthreads();
+  {  // exclusive prefix over warps for digit = threadIdx.x
+    uint32_t run = 0;
+#pragma unroll
+    for (int ww = 0; ww < kWarps; ++ww) {
+      const uint32_t c = s_cnt[ww][threadIdx.x];
+      s_cnt[ww][threadIdx.x] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = wbase + j * 32 + lane;
+    if (idx < N) {
+      const uint32_t d = (key[j] >> shift) & (kBins - 1);
+      const uint32_t pos = s_base[d] + s_cnt[w][d] + rank[j];
+      keys_out[so + pos] = key[j];
+      vals_out[so + pos] = val[j];
+    }
+  }
+}
+
+// ---- 4. Jaccard gradient + dot --------------------------------------------------------------------
+__global__ void __launch_bounds__(kSortThreads)
+lovasz_fgcount_kernel(const uint32_t* __restrict__ vals, const uint8_t* __restrict__ ylab, int N, int tiles,
+                      const int* __restrict__ class_count, int* __restrict__ tile_fg) {
+  const int seg = blockIdx.y, tile = blockIdx.x;
+  if (class_count[seg] == 0) return;
+  int c = 0;
+  const int base = tile * kSortTile + threadIdx.x * kKeysPerThread;
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = base + j;
+    if (idx < N) c += (ylab[vals[(int64_t)seg * N + idx]] == seg);
+  }
+  __shared__ int s_warp[9];
+  int tot;
+  block_excl_scan256(c, s_warp, &tot);
+  if (threadIdx.x == 0) tile_fg[seg * tiles + tile] = tot;
+}
+
+__global__ void __launch_bounds__(256)
+lovasz_tilescan_kernel(int* __restrict__ tile_fg, int tiles, const int* __restrict__ class_count) {
+  const int seg = blockIdx.x;
+  if (class_count[seg] == 0) return;
+  __shared__ int s_warp[9];
+  int* t = tile_fg + seg * tiles;
+  int carry = 0;
+  for (int base = 0; base < tiles; base += 256) {
+    const int i = base + threadIdx.x;
+    const int v = i < tiles ? t[i] : 0;
+    int tot;
+    const int e = block_excl_scan256(v, s_warp, &tot);
+    if (i < tiles) t[i] = carry + e;
+    carry += tot;
+  }
+}
+
+__device__ __forceinline__ float jaccard_at(int G, int k /*0-based position*/, int cf /*inclusive fg count*/) {
+  // lovasz_grad: 1 - (gts - cumsum(fg)) / (gts + cumsum(1 - fg)); every operand is an exact fp32 integer
+  const float inter = (float)(G - cf);
+  const float uni = (float)(G + (k + 1 - cf));
+  return __fsub_rn(1.f, __fdiv_rn(inter, uni));
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+lovasz_grad_dot_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                       const uint8_t* __restrict__ ylab, int N, int tiles,
+                       const int* __restrict__ class_count, const int* __restrict__ tile_fg,
+                       float* __restrict__ dprob, double* __restrict__ acc) {
+  const int seg = blockIdx.y, tile = blockIdx.x;
+  const int G = class_count[seg];
+  if (G == 0) return;
+  __shared__ int s_warp[9];
+  __shared__ double s_red[8];
+  const int base = tile * kSortTile + threadIdx.x * kKeysPerThread;
+  uint32_t v[kKeysPerThread];
+  int fg[kKeysPerThread], c = 0;
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = base + j;
+    v[j] = idx < N ? vals[(int64_t)seg * N + idx] : 0u;
+    fg[j] = idx < N ? (ylab[v[j]] == seg) : 0;
+    c += fg[j];
+  }
+  int tot;
+  int cf = tile_fg[seg * tiles + tile] + block_excl_scan256(c, s_warp, &tot);  // fg count before my first key
+  double dot = 0.0;
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = base + j;
+    if (idx < N) {
+      const int cf_prev = cf;
+      cf += fg[j];
+      const float jac = jaccard_at(G, idx, cf);
+      const float g = idx == 0 ? jac : __fsub_rn(jac, jaccard_at(G, idx - 1, cf_prev));
+      const float err = __uint_as_float(kOneBits - keys[(int64_t)seg * N + idx]);
+      dot += (double)err * (double)g;
+      // d|fg - p| / dp = -sign(fg - p), sign(0) = 0
+      const float sgn = err == 0.f ? 0.f : (fg[j] ? -1.f : 1.f);
+      dprob[(int64_t)v[j] * kC + seg] = g * sgn;
+    }
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+  if (lane == 0) s_red[wid] = dot;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0;
+    for (int i = 0; i < 8; ++i) a += s_red[i];
+    atomicAdd(acc + 2 + seg, a);
+  }
+}
+
+// ---- 5. scalars and backward ----------------------------------------------------------------------
+__global__ void cels_finalize_kernel(CelsWs ws, float lambda, float* __restrict__ out) {
+  int n_present = 0;
+  double lov = 0.0;
+  for (int c = 0; c < kC; ++c)
+    if (ws.class_count[c] > 0) { n_present++; lov += ws.acc[2 + c]; }
+  // mean() helper of lovasz_losses.py:232-250: acc / n  (n == 1 returns acc itself)
+  const float lovasz = n_present > 0 ? (float)(lov / n_present) : 0.f;
+  const float ce = (float)(ws.acc[0] / ws.acc[1]);  // 0/0 = NaN on an empty selection, like torch
+  out[0] = ce + lambda * lovasz;
+  out[1] = ce;
+  out[2] = lovasz;
+  out[3] = (float)n_present;
+}
+
+__global__ void __launch_bounds__(256)
+cels_backward_kernel(CelsWs ws, const float* __restrict__ class_w, float lambda, float* __restrict__ dlogits) {
+  const int N = *ws.n_valid;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  int n_present = 0;
+#pragma unroll
+  for (int c = 0; c < kC; ++c) n_present += ws.class_count[c] > 0;
+  const float lscale = n_present > 0 ? lambda / (float)n_present : 0.f;
+  const float wsum = (float)ws.acc[1];
+  const int y = ws.ylab[i];
+  const float wy = y < kC ? __ldg(class_w + y) / wsum : 0.f;
+  float p[kC], dp[kC], s = 0.f;
+  const float4* ps = reinterpret_cast<const float4*>(ws.probs + (int64_t)i * kC);
+  const float4* ds = reinterpret_cast<const float4*>(ws.dprob + (int64_t)i * kC);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float4 a = ps[q], b = ds[q];
+    p[4 * q] = a.x; p[4 * q + 1] = a.y; p[4 * q + 2] = a.z; p[4 * q + 3] = a.w;
+    dp[4 * q] = b.x * lscale; dp[4 * q + 1] = b.y * lscale; dp[4 * q + 2] = b.z * lscale; dp[4 * q + 3] = b.w * lscale;
+  }
+#pragma unroll
+  for (int c = 0; c < kC; ++c) s += dp[c] * p[c];
+  float g[kC];
+#pragma unroll
+  for (int c = 0; c < kC; ++c) g[c] = p[c] * (dp[c] - s) + wy * (p[c] - (c == y ? 1.f : 0.f));
+  float4* out = reinterpret_cast<float4*>(dlogits + (int64_t)ws.rows[i] * kC);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) out[q] = make_float4(g[4 * q], g[4 * q + 1], g[4 * q + 2], g[4 * q + 3]);
+}
+
+}  // namespace tdssf
+
+extern "C" size_t tdssf_cels_workspace_bytes(int64_t n_rows) {
+  if (n_rows < 0) n_rows = 0;
+  return tdssf::carve(nullptr, nullptr, std::max<int64_t>(n_rows, 1));
+}
+
+extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, const uint8_t* mask,
+                                  int64_t n_rows, const float* class_w, float lambda_lovasz, int ignore_index,
+                                  float* out_scalars, int64_t* n_valid_host, int64_t* preds, int64_t* gt,
+                                  float* dlogits, void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace tdssf;
+  TDSSF_REQUIRE(n_rows >= 0 && n_rows < (int64_t)1 << 27, "tdssf_cels_fwd_bwd: n_rows=%lld out of range", (long long)n_rows);
+  TDSSF_REQUIRE(out_scalars && n_valid_host && class_w && workspace, "tdssf_cels_fwd_bwd: NULL pointer");
+  TDSSF_REQUIRE(workspace_bytes >= tdssf_cels_workspace_bytes(n_rows), "tdssf_cels_fwd_bwd: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  CelsWs ws;
+  char* base = reinterpret_cast<char*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  carve(&ws, base, std::max<int64_t>(n_rows, 1));
+  TDSSF_CUDA(cudaMemsetAsync(ws.n_valid, 0, sizeof(int), s));
+  TDSSF_CUDA(cudaMemsetAsync(ws.class_count, 0, kC * sizeof(int), s));
+  TDSSF_CUDA(cudaMemsetAsync(ws.acc, 0, 18 * sizeof(double), s));
+  if (dlogits && n_rows) TDSSF_CUDA(cudaMemsetAsync(dlogits, 0, (size_t)n_rows * kC * sizeof(float), s));
+  *n_valid_host = 0;
+  if (n_rows > 0) {
+    TDSSF_REQUIRE(logits && labels && preds && gt, "tdssf_cels_fwd_bwd: NULL input/output");
+    TDSSF_REQUIRE(((uintptr_t)logits & 15) == 0 && (!dlogits || ((uintptr_t)dlogits & 15) == 0),
+                  "tdssf_cels_fwd_bwd: logits/dlogits must be 16-byte aligned");
+    const unsigned row_tiles = (unsigned)ceil_div(n_rows, kRowTile);
+    cels_count_kernel<<<row_tiles, kRowTile, 0, s>>>(labels, mask, n_rows, ignore_index, ws.tile_count);
+    TDSSF_LAUNCH_CHECK();
+    scan_ints_kernel<<<1, 256, 0, s>>>(ws.tile_count, ws.tile_offset, row_tiles, ws.n_valid);
+    TDSSF_LAUNCH_CHECK();
+    int n_valid = 0;
+    TDSSF_CUDA(cudaMemcpyAsync(&n_valid, ws.n_valid, sizeof(int), cudaMemcpyDeviceToHost, s));
+    TDSSF_CUDA(cudaStreamSynchronize(s));  // the reference's boolean indexing synchronises here as well
+    *n_valid_host = n_valid;
+    if (n_valid > 0) {
+      const int N = n_valid;
+      cels_compact_kernel<<<row_tiles, kRowTile, 0, s>>>(logits, labels, mask, n_rows, ignore_index, class_w, ws, preds, gt);
+      TDSSF_LAUNCH_CHECK();
+      const int tiles = (int)ceil_div(N, kSortTile);
+      const dim3 sgrid((unsigned)tiles, kC);
+      int cur = 0;
+      for (int pass = 0; pass < kPasses; ++pass) {
+        const int shift = pass * kRadixBits;
+        sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, shift, tiles, ws.class_count, ws.hist);
+        TDSSF_LAUNCH_CHECK();
+        sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count);
+        TDSSF_LAUNCH_CHECK();
+        sort_scatter_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1],
+                                                           N, shift, tiles, ws.class_count, ws.hist);
+        TDSSF_LAUNCH_CHECK();
+        cur ^= 1;
+      }
+      TDSSF_CUDA(cudaMemsetAsync(ws.dprob, 0, (size_t)N * kC * sizeof(float), s));
+      lovasz_fgcount_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.vals[cur], ws.ylab, N, tiles, ws.class_count, ws.tile_fg);
+      TDSSF_LAUNCH_CHECK();
+      lovasz_tilescan_kernel<<<kC, 256, 0, s>>>(ws.tile_fg, tiles, ws.class_count);
+      TDSSF_LAUNCH_CHECK();
+      lovasz_grad_dot_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.ylab, N, tiles, ws.class_count,
+                                                            ws.tile_fg, ws.dprob, ws.acc);
+      TDSSF_LAUNCH_CHECK();
+      if (dlogits) {
+        cels_backward_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, s>>>(ws, class_w, lambda_lovasz, dlogits);
+        TDSSF_LAUNCH_CHECK();
+      }
+    }
+  }
+  cels_finalize_kernel<<<1, 1, 0, s>>>(ws, lambda_lovasz, out_scalars);
+  TDSSF_LAUNCH_CHECK();
+  return TDSSF_OK;
+}

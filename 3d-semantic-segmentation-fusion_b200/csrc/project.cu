@@ -1,6 +1,7 @@
 // a1+a2+a3: multi-camera projection, depth/bounds mask, pixel rescale and patch index.
 // One thread per LiDAR point, the six cameras unrolled in registers; calibration of the sweep lives
 // in shared memory.  HBM-bound: 16 B in, 94 B out (reference layout) or 16 B out (records).
+#include <algorithm>
 #include "project.cuh"
 
 namespace tdssf {
@@ -64,7 +65,36 @@ project_kernel(const float* __restrict__ xyz, int64_t sweep_stride, int64_t poin
   }
 }
 
+// a2 stand-alone: out = pix * (W_new/W_orig, H_new/H_orig), one float2 per thread.
+__global__ void scale_pixels_kernel(const float2* __restrict__ pix, const float* __restrict__ img_hw, int hw_rows,
+                                    int64_t per_sweep, int64_t total, float new_h, float new_w,
+                                    float2* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int b = hw_rows == 1 ? 0 : (int)(i / per_sweep);
+    const float sh = __fdiv_rn(new_h, fmaxf(__ldg(img_hw + 2 * b), 1e-6f));
+    const float sw = __fdiv_rn(new_w, fmaxf(__ldg(img_hw + 2 * b + 1), 1e-6f));
+    const float2 q = pix[i];
+    out[i] = make_float2(__fmul_rn(q.x, sw), __fmul_rn(q.y, sh));
+  }
+}
+
 }  // namespace tdssf
+
+extern "C" int tdssf_scale_pixels(const float* pix, const float* img_hw, int hw_rows, int B, int64_t per_sweep,
+                                  float new_h, float new_w, float* out, void* stream) {
+  using namespace tdssf;
+  TDSSF_REQUIRE(pix && img_hw && out, "tdssf_scale_pixels: NULL pointer");
+  TDSSF_REQUIRE(hw_rows == 1 || hw_rows == B, "tdssf_scale_pixels: origin sizes have %d rows for a batch of %d", hw_rows, B);
+  TDSSF_REQUIRE((((uintptr_t)pix | (uintptr_t)out) & 7) == 0, "tdssf_scale_pixels: 8-byte alignment required");
+  const int64_t total = (int64_t)B * per_sweep;
+  if (total <= 0) return TDSSF_OK;
+  const unsigned blocks = (unsigned)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 16);
+  scale_pixels_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float2*>(pix), img_hw, hw_rows,
+                                                                per_sweep, total, new_h, new_w,
+                                                                reinterpret_cast<float2*>(out));
+  TDSSF_LAUNCH_CHECK();
+  return TDSSF_OK;
+}
 
 extern "C" int tdssf_project(const float* xyz, int64_t sweep_stride, int64_t point_stride,
                              const float* K, const float* Rt, const float* img_hw, int B, int V,

@@ -1,0 +1,335 @@
+"""torch-facing wrappers of the C ABI (include/tdssf.h).
+
+PyTorch is plumbing here: device memory, streams, autograd bookkeeping.  Every op launches the
+hand-written sm_100a kernels of libtdssf.so through ctypes and raises if the tensors are not on a
+CUDA device — there is no CPU or eager fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import lib, check
+
+_TOK_DTYPES = {torch.float32: _lib.F32, torch.float16: _lib.F16, torch.bfloat16: _lib.BF16}
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream(t: torch.Tensor):
+    return C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("tdssf ops run on CUDA tensors only (no CPU fallback); got a tensor on " + str(t.device))
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.to(torch.float32).contiguous()
+
+
+# ------------------------------------------------------------------------------------------------
+# calibration stacking: mirrors multi_camera_projector's `_to_tensor` (utils/fusion_model.py:36-49)
+# ------------------------------------------------------------------------------------------------
+def stack_calibration(cam_intrinsics: Sequence, lidar2cam_extrinsics: Sequence, device) -> tuple[torch.Tensor, torch.Tensor]:
+    n_cam = cam_intrinsics[0].shape[0]
+
+    def to_tensor(data, tail):
+        items = []
+        for item in data:
+            if not torch.is_tensor(item):
+                items.append(torch.as_tensor(item, dtype=torch.float32))
+            else:
+                items.append(item.to(dtype=torch.float32))
+        # one host-side stack + one copy instead of a copy per sweep
+        if all(not i.is_cuda for i in items):
+            stacked = torch.stack(items, dim=0).to(device, non_blocking=True)
+        else:
+            stacked = torch.stack([i.to(device) for i in items], dim=0)
+        if tuple(stacked.shape[1:]) != tail:
+            raise ValueError(f"Expected shape (*, {tail}) but got {tuple(stacked.shape)}.")
+        return stacked.contiguous()
+
+    K = to_tensor(cam_intrinsics, (n_cam, 3, 3))
+    Rt = to_tensor(lidar2cam_extrinsics, (n_cam, 4, 4))
+    return K, Rt
+
+
+def image_sizes_f32(image_sizes, B: int, device) -> torch.Tensor:
+    hw = torch.as_tensor(image_sizes, dtype=torch.float32, device=device)
+    if tuple(hw.shape) != (B, 2):
+        raise ValueError("image_sizes must be of shape (B, 2) where each entry is (H, W).")
+    return hw.contiguous()
+
+
+def _points_layout(points: torch.Tensor):
+    """(B,V,>=3) fp32 view with unit inner stride -> (tensor kept alive, sweep_stride, point_stride)."""
+    if points.dtype != torch.float32 or points.stride(-1) != 1 or points.dim() != 3:
+        points = points.to(torch.float32).contiguous()
+    B, V, _ = points.shape
+    ss = points.stride(0) if B > 1 else points.stride(1) * V
+    return points, ss, points.stride(1)
+
+
+# ------------------------------------------------------------------------------------------------
+# a1-a3
+# ------------------------------------------------------------------------------------------------
+def project(points, K, Rt, img_hw, encoder=None, *, want_pix=True, want_depth=True, want_valid=True,
+            want_flat=False, want_rec=False):
+    """points (B,V,>=3) CUDA fp32 (may be a strided view of (B,V,4)); K (B,NC,3,3); Rt (B,NC,4,4);
+    img_hw (B,2) fp32.  Returns dict with the requested outputs."""
+    _need_cuda(points, K, Rt, img_hw)
+    pts, ss, ps = _points_layout(points)
+    B, V, _ = pts.shape
+    NC = K.shape[1]
+    dev = pts.device
+    out = {}
+    pix = torch.empty((B, NC, V, 2), dtype=torch.float32, device=dev) if want_pix else None
+    depth = torch.empty((B, NC, V), dtype=torch.float32, device=dev) if want_depth else None
+    valid = torch.empty((B, NC, V), dtype=torch.uint8, device=dev) if want_valid else None
+    flat = torch.empty((B, NC, V), dtype=torch.int32, device=dev) if want_flat else None
+    rec = torch.empty((B, V, 4), dtype=torch.int32, device=dev) if want_rec else None
+    rh = rw = ps_ = 0
+    if want_flat or want_rec:
+        if encoder is None:
+            raise ValueError("patch indices need the encoder's patch_size / resize_height / resize_width")
+        rh, rw, ps_ = int(encoder.resize_height), int(encoder.resize_width), int(encoder.patch_size)
+    check(lib.tdssf_project(_ptr(pts), ss, ps, _ptr(_f32c(K)), _ptr(_f32c(Rt)), _ptr(_f32c(img_hw)), B, V, NC,
+                            rh, rw, ps_, _ptr(pix), _ptr(depth), _ptr(valid), _ptr(flat), _ptr(rec), _stream(pts)),
+          "tdssf_project")
+    out.update(pix=pix, depth=depth, valid=valid, flat_idx=flat, rec=rec)
+    return out
+
+
+def scale_pixels(pixel_coords: torch.Tensor, origin_hw: torch.Tensor, new_h: float, new_w: float) -> torch.Tensor:
+    """pixel_coords (B,...,2) CUDA fp32; origin_hw (B,2) or (1,2) fp32 on the same device."""
+    _need_cuda(pixel_coords, origin_hw)
+    pix = _f32c(pixel_coords)
+    hw = _f32c(origin_hw)
+    B = pix.shape[0]
+    per_sweep = pix.numel() // (2 * B) if B else 0
+    out = torch.empty_like(pix)
+    check(lib.tdssf_scale_pixels(_ptr(pix), _ptr(hw), hw.shape[0], B, per_sweep, float(new_h), float(new_w), _ptr(out),
+                                 _stream(pix)), "tdssf_scale_pixels")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# a4-a5
+# ------------------------------------------------------------------------------------------------
+def gather_mean(tokens: torch.Tensor, rec: torch.Tensor) -> torch.Tensor:
+    """tokens (B,NC,M,Ci) CUDA fp32/fp16/bf16; rec (B,V,4) int32 records -> (B,V,Ci) fp32."""
+    _need_cuda(tokens, rec)
+    if tokens.dtype not in _TOK_DTYPES:
+        tokens = tokens.float()
+    tokens = tokens.contiguous()
+    B, NC, M, Ci = tokens.shape
+    V = rec.shape[1]
+    feat = torch.empty((B, V, Ci), dtype=torch.float32, device=tokens.device)
+    check(lib.tdssf_gather_mean(_ptr(tokens), _TOK_DTYPES[tokens.dtype], _ptr(rec), B, V, NC, M, Ci, _ptr(feat),
+                                _stream(tokens)), "tdssf_gather_mean")
+    return feat
+
+
+# ------------------------------------------------------------------------------------------------
+# a6: fp32 CUDA-core MLP with autograd, and the tensor-core paths
+# ------------------------------------------------------------------------------------------------
+def _weights_struct(params: Sequence[torch.Tensor]) -> _lib.MlpWeights:
+    W1, b1, W2, b2, W3, b3 = params
+    if tuple(W1.shape) != (256, 448) or tuple(W2.shape) != (64, 256) or tuple(W3.shape) != (16, 64):
+        raise ValueError("tdssf MLP kernels are built for the reference shape 448->256->64->16 "
+                         f"(got {tuple(W1.shape)}, {tuple(W2.shape)}, {tuple(W3.shape)})")
+    return _lib.MlpWeights(*[t.data_ptr() for t in (W1, b1, W2, b2, W3, b3)])
+
+
+class _MlpF32(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_pt, x_img, W1, b1, W2, b2, W3, b3):
+        _need_cuda(x_pt, x_img, W1)
+        shape = x_pt.shape[:-1]
+        xp = _f32c(x_pt).reshape(-1, 64)
+        xi = _f32c(x_img).reshape(-1, 384)
+        params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
+        N = xp.shape[0]
+        dev = xp.device
+        h1 = torch.empty((N, 256), dtype=torch.float32, device=dev)
+        h2 = torch.empty((N, 64), dtype=torch.float32, device=dev)
+        logits = torch.empty((N, 16), dtype=torch.float32, device=dev)
+        ws = _weights_struct(params)
+        check(lib.tdssf_mlp_fwd_f32(_ptr(xp), _ptr(xi), N, C.byref(ws), _ptr(h1), _ptr(h2), _ptr(logits), _stream(xp)),
+              "tdssf_mlp_fwd_f32")
+        ctx.save_for_backward(xp, xi, h1, h2, *params)
+        ctx.in_shape = tuple(x_pt.shape)
+        return logits.reshape(*shape, 16)
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        xp, xi, h1, h2, W1, b1, W2, b2, W3, b3 = ctx.saved_tensors
+        N = xp.shape[0]
+        dev = xp.device
+        dl = _f32c(dlogits).reshape(-1, 16)
+        grads = [torch.zeros_like(t) for t in (W1, b1, W2, b2, W3, b3)]
+        dx_pt = torch.empty((N, 64), dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
+        ws_bytes = lib.tdssf_mlp_bwd_workspace_bytes(N)
+        work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        w = _weights_struct([W1, b1, W2, b2, W3, b3])
+        g = _lib.MlpGrads(*[t.data_ptr() for t in grads])
+        check(lib.tdssf_mlp_bwd_f32(_ptr(xp), _ptr(xi), _ptr(h1), _ptr(h2), _ptr(dl), N, C.byref(w), C.byref(g),
+                                    _ptr(dx_pt), _ptr(work), ws_bytes, _stream(xp)), "tdssf_mlp_bwd_f32")
+        return (dx_pt.reshape(ctx.in_shape) if dx_pt is not None else None, None, *grads)
+
+
+def mlp_f32(x_pt, x_img, W1, b1, W2, b2, W3, b3):
+    """fp32 parity mode of the fusion MLP, differentiable w.r.t. x_pt and the six parameters."""
+    return _MlpF32.apply(x_pt, x_img, W1, b1, W2, b2, W3, b3)
+
+
+def pack_weights(W1, b1, W2, b2, W3, b3) -> torch.Tensor:
+    """bf16 tensor-core operand image of the MLP weights (both CTA ranks + biases)."""
+    _need_cuda(W1)
+    params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
+    packed = torch.empty(lib.tdssf_mlp_pack_bytes(), dtype=torch.uint8, device=W1.device)
+    ws = _weights_struct(params)
+    check(lib.tdssf_mlp_pack_weights(C.byref(ws), _ptr(packed), _stream(W1)), "tdssf_mlp_pack_weights")
+    return packed
+
+
+def mlp_tc(x_pt, x_img, packed) -> torch.Tensor:
+    """tcgen05 MLP on pre-gathered fp32 features: (N,64),(N,384) -> (N,16)."""
+    _need_cuda(x_pt, x_img, packed)
+    shape = x_pt.shape[:-1]
+    xp = _f32c(x_pt).reshape(-1, 64)
+    xi = _f32c(x_img).reshape(-1, 384)
+    N = xp.shape[0]
+    logits = torch.empty((N, 16), dtype=torch.float32, device=xp.device)
+    check(lib.tdssf_mlp_fwd_tc(_ptr(xp), _ptr(xi), N, _ptr(packed), _ptr(logits), _stream(xp)), "tdssf_mlp_fwd_tc")
+    return logits.reshape(*shape, 16)
+
+
+def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None):
+    """Fully fused inference: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) -> logits (B,V,16)."""
+    _need_cuda(points, K, Rt, img_hw, tokens, x_pt, packed)
+    pts, ss, ps = _points_layout(points)
+    B, V, _ = pts.shape
+    if tokens.dtype not in _TOK_DTYPES:
+        tokens = tokens.float()
+    tokens = tokens.contiguous()
+    _, NC, M, Ci = tokens.shape
+    xp = _f32c(x_pt)
+    logits = out if out is not None else torch.empty((B, V, 16), dtype=torch.float32, device=pts.device)
+    rec = torch.empty((B, V, 4), dtype=torch.int32, device=pts.device) if want_rec else None
+    check(lib.tdssf_fusion_fwd(_ptr(pts), ss, ps, _ptr(_f32c(K)), _ptr(_f32c(Rt)), _ptr(_f32c(img_hw)), B, V, NC,
+                               int(encoder.resize_height), int(encoder.resize_width), int(encoder.patch_size),
+                               _ptr(tokens), _TOK_DTYPES[tokens.dtype], M, Ci, _ptr(xp), _ptr(packed), _ptr(logits),
+                               _ptr(rec), _stream(pts)), "tdssf_fusion_fwd")
+    return (logits, rec) if want_rec else logits
+
+
+# ------------------------------------------------------------------------------------------------
+# a7
+# ------------------------------------------------------------------------------------------------
+def devox_nn(pts: torch.Tensor, vox: torch.Tensor) -> torch.Tensor:
+    """pts (B,P,>=3), vox (B,V,>=3) CUDA fp32 -> (B,P) int64 nearest-voxel indices."""
+    _need_cuda(pts, vox)
+    pts = _f32c(pts)
+    vox = _f32c(vox)
+    B, P, sp = pts.shape
+    V, sv = vox.shape[1], vox.shape[2]
+    idx = torch.empty((B, P), dtype=torch.int64, device=pts.device)
+    check(lib.tdssf_devox_nn(_ptr(pts), sp, _ptr(vox), sv, B, P, V, _ptr(idx), _stream(pts)), "tdssf_devox_nn")
+    return idx
+
+
+class _DevoxGather(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, scores, idx):
+        _need_cuda(scores, idx)
+        s = _f32c(scores)
+        B, V, Cn = s.shape
+        P = idx.shape[1]
+        out = torch.empty((B, P, Cn), dtype=torch.float32, device=s.device)
+        check(lib.tdssf_devox_gather(_ptr(s), _ptr(idx), B, P, V, Cn, _ptr(out), _stream(s)), "tdssf_devox_gather")
+        ctx.save_for_backward(idx)
+        ctx.shape = (B, P, V, Cn)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (idx,) = ctx.saved_tensors
+        B, P, V, Cn = ctx.shape
+        d = _f32c(dout)
+        ds = torch.zeros((B, V, Cn), dtype=torch.float32, device=d.device)
+        check(lib.tdssf_devox_scatter_add(_ptr(d), _ptr(idx), B, P, V, Cn, _ptr(ds), _stream(d)),
+              "tdssf_devox_scatter_add")
+        return ds, None
+
+
+def devox_gather(scores: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    return _DevoxGather.apply(scores, idx)
+
+
+# ------------------------------------------------------------------------------------------------
+# a8-a10
+# ------------------------------------------------------------------------------------------------
+class _Cels(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, mask, class_w, lam, ignore_index):
+        _need_cuda(logits, labels)
+        x = _f32c(logits).reshape(-1, 16)
+        n_rows = x.shape[0]
+        dev = x.device
+        lab = labels.reshape(-1).to(torch.int64).contiguous()
+        m = None if mask is None else mask.reshape(-1).to(torch.uint8).contiguous()
+        w = _f32c(class_w.to(dev))
+        scal = torch.empty(4, dtype=torch.float32, device=dev)
+        preds = torch.empty(max(n_rows, 1), dtype=torch.int64, device=dev)
+        gt = torch.empty(max(n_rows, 1), dtype=torch.int64, device=dev)
+        need_grad = ctx.needs_input_grad[0]
+        dlog = torch.empty_like(x) if need_grad else None
+        ws_bytes = lib.tdssf_cels_workspace_bytes(n_rows)
+        work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        n_valid = C.c_int64(0)
+        check(lib.tdssf_cels_fwd_bwd(_ptr(x), _ptr(lab), _ptr(m), n_rows, _ptr(w), float(lam), int(ignore_index),
+                                     _ptr(scal), C.byref(n_valid), _ptr(preds), _ptr(gt), _ptr(dlog), _ptr(work),
+                                     ws_bytes, _stream(x)), "tdssf_cels_fwd_bwd")
+        n = int(n_valid.value)
+        ctx.dlog = dlog
+        ctx.in_shape = tuple(logits.shape)
+        ctx.mark_non_differentiable(preds, gt)
+        return scal[0].clone(), scal[1].clone(), scal[2].clone(), preds[:n], gt[:n]
+
+    @staticmethod
+    def backward(ctx, g_total, g_ce, g_lov, _gp, _gg):
+        # The kernel produced d total / d logits; ce and lovasz are returned for logging only
+        # (the reference loops call backward on total_loss, utils/train.py:91).
+        d = ctx.dlog
+        if d is None:
+            return None, None, None, None, None, None
+        return (d * g_total).reshape(ctx.in_shape), None, None, None, None, None
+
+
+def cels(logits, labels, mask, class_w, lam=1.0, ignore_index=0):
+    """(total, ce, lovasz, predictions, gt_valid); `total.backward()` reaches `logits`."""
+    return _Cels.apply(logits, labels, mask, class_w, lam, ignore_index)
+
+
+# ------------------------------------------------------------------------------------------------
+# a11
+# ------------------------------------------------------------------------------------------------
+def confusion(preds: torch.Tensor, labels: torch.Tensor, num_classes: int, out: Optional[torch.Tensor] = None):
+    """int64 (C,C) confusion matrix, rows = truth; accumulates into `out` when given."""
+    _need_cuda(preds, labels)
+    p = preds.reshape(-1).to(torch.int64).contiguous()
+    l = labels.reshape(-1).to(torch.int64).contiguous()
+    if p.numel() != l.numel():
+        raise ValueError("preds and labels must have the same number of elements")
+    cm = out if out is not None else torch.zeros((num_classes, num_classes), dtype=torch.int64, device=p.device)
+    check(lib.tdssf_confusion(_ptr(p), _ptr(l), p.numel(), num_classes, _ptr(cm), _stream(p)), "tdssf_confusion")
+    return cm

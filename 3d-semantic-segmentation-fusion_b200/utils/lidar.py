@@ -1,0 +1,96 @@
+"""Drop-in for the reference's utils/lidar.py (LiDARFeatureEncoder, utils/lidar.py:14-172).
+
+In scope here: the padding / caching contract of `forward` and `devoxelize` (nearest voxel per raw
+point, gather, differentiable through the gathered scores), which runs on libtdssf.so
+(csrc/devox.cu).  The PTv3 backbone and the Open3D voxelizer stay stock third-party code exactly as
+in the reference: they are imported lazily, and a caller may inject replacements (`backbone=`,
+`voxelizer=`) — the synthetic harness does, because neither open3d nor spconv exists in this image.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from tdssf import ops
+
+
+class LiDARFeatureEncoder(nn.Module):
+    """LiDAR -> voxelize -> PTv3 -> per-voxel feature (V x 64); devoxelize maps voxel scores to points."""
+
+    def __init__(self, config, backbone: nn.Module | None = None, voxelizer=None):
+        super().__init__()
+        self.voxel_size = config['dataset_params']['lidar']['voxel_size']
+        if backbone is None:
+            try:  # the reference's stock backbone (utils/lidar.py:12,25)
+                from PointTransformerV3.model import PointTransformerV3
+            except Exception as exc:  # spconv / torch_scatter / flash_attn / addict / timm
+                raise ImportError("PointTransformerV3 (and its spconv/torch_scatter dependencies) is required for the "
+                                  "stock backbone; pass backbone= to use another module") from exc
+            backbone = PointTransformerV3(in_channels=4)
+        self.ptv3 = backbone
+        self._voxelizer = voxelizer
+
+    def forward(self, lidar_points):
+        """lidar_points (B,P,4) -> voxel_features (B,V_max,64), voxel_raw (B,V_max,4), voxel_coords (B,V_max,3) int32,
+        voxel_mask (B,V_max) bool.  Caches `lidar_points_raw` and `voxel_raw` for devoxelize (:37,79)."""
+        self.lidar_points_raw = lidar_points
+        dev = lidar_points.device
+        feats, raws, coords = [], [], []
+        for cloud in lidar_points:
+            voxel_raw, voxel_coords = self.voxelize_open3d(cloud)
+            sample = {"coord": voxel_raw[:, :3], "feat": voxel_raw,
+                      "grid_size": torch.tensor(self.voxel_size, device=dev),
+                      "batch": torch.zeros(voxel_raw.shape[0], dtype=torch.long, device=dev)}
+            out = self.ptv3(sample)
+            feats.append(out.feat if hasattr(out, "feat") else out)
+            raws.append(voxel_raw)
+            coords.append(voxel_coords)
+        B = len(feats)
+        v_max = max(f.shape[0] for f in feats)
+        voxel_features = torch.zeros((B, v_max, feats[0].shape[1]), device=dev)
+        voxel_raw_t = torch.zeros((B, v_max, 4), device=dev)
+        voxel_coords_t = torch.zeros((B, v_max, 3), device=dev, dtype=torch.int)
+        voxel_mask = torch.zeros((B, v_max), device=dev, dtype=torch.bool)
+        for i, (f, r, c) in enumerate(zip(feats, raws, coords)):
+            n = f.shape[0]
+            voxel_features[i, :n] = f
+            voxel_raw_t[i, :n] = r
+            voxel_coords_t[i, :n] = c
+            voxel_mask[i, :n] = True
+        self.voxel_raw = voxel_raw_t  # zero padding included: devoxelize searches all V_max rows
+        return voxel_features, voxel_raw_t, voxel_coords_t, voxel_mask
+
+    def voxelize_open3d(self, lidar_points):
+        """(P,4) -> voxel_raw (V,4) [centroid xyz, 5-NN weighted intensity], voxel_coords (V,3) int32.
+        Stock Open3D + scikit-learn like the reference (utils/lidar.py:83-118) unless a voxelizer was injected."""
+        if self._voxelizer is not None:
+            return self._voxelizer(lidar_points, self.voxel_size)
+        try:
+            import open3d as o3d
+            from sklearn.neighbors import NearestNeighbors
+        except Exception as exc:
+            raise ImportError("open3d and scikit-learn are required for the stock voxelizer; pass voxelizer=") from exc
+        pts = lidar_points.detach().cpu().numpy()
+        cloud = o3d.geometry.PointCloud()
+        cloud.points = o3d.utility.Vector3dVector(pts[:, :3])
+        centres = np.asarray(cloud.voxel_down_sample(voxel_size=self.voxel_size).points)
+        if pts.shape[1] == 4:
+            _, nbr = NearestNeighbors(n_neighbors=5, algorithm="auto").fit(pts[:, :3]).kneighbors(centres)
+            w = np.array([0.4, 0.3, 0.2, 0.05, 0.05]).reshape(1, 5)
+            raw = np.hstack([centres, (pts[nbr.squeeze(), 3] * w).sum(axis=1).reshape(-1, 1)])
+        else:
+            raw = centres
+        grid = np.floor(centres / self.voxel_size).astype(np.int32)
+        return (torch.from_numpy(raw).float().to(lidar_points.device),
+                torch.from_numpy(grid).int().to(lidar_points.device))
+
+    def devoxelize(self, voxel_scores):
+        """voxel_scores (B,V_max,C) -> (point_scores (B,P,C), voxel_indices (B,P) int64); gradients flow to
+        voxel_scores through the gather (backward = scatter-add)."""
+        pts = self.lidar_points_raw
+        vox = self.voxel_raw
+        if pts.dim() != 3 or vox.shape[0] != voxel_scores.shape[0]:
+            raise RuntimeError("devoxelize must follow forward() on the same batch (it reads the cached clouds)")
+        idx = ops.devox_nn(pts.to(voxel_scores.device), vox.to(voxel_scores.device))
+        return ops.devox_gather(voxel_scores, idx), idx

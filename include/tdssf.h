@@ -92,6 +92,12 @@ TDSSF_API int tdssf_project(const float* xyz, int64_t sweep_stride, int64_t poin
                   float* pix, float* depth, uint8_t* valid, int32_t* flat_idx, tdssf_rec* rec,
                   void* stream);
 
+/* a2 stand-alone   replaces scale_pixel_coords   utils/fusion_model.py:89-127
+ * pix/out [B, per_sweep, 2] fp32 (u,v); img_hw [hw_rows,2] fp32 (H,W) with hw_rows == B or 1 (broadcast);
+ * out = pix * (new_w / max(W,1e-6), new_h / max(H,1e-6)), scales computed in fp32 like the reference. */
+TDSSF_API int tdssf_scale_pixels(const float* pix, const float* img_hw, int hw_rows, int B, int64_t per_sweep,
+                       float new_h, float new_w, float* out, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * a4+a5  per-camera patch-token gather and masked mean over cameras
  * replaces  utils/fusion_model.py:184-201

@@ -1,0 +1,115 @@
+"""GPU parity tests of the tcgen05 (bf16 operands, fp32 accumulate) kernels.  Tolerance 1e-2 relative to the
+largest |logit| (north_star's bf16-MLP bound); integer by-products (camera records) are bit-exact."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import np_oracle as O  # noqa: E402
+from tdssf import synth  # noqa: E402
+
+BF16_TOL = 1e-2
+W_KEYS = ("mlp.0.weight", "mlp.0.bias", "mlp.2.weight", "mlp.2.bias", "mlp.4.weight", "mlp.4.bias")
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from tdssf import ops as _ops, _lib
+    _lib.check(_lib.lib.tdssf_check_device(), "device")
+    return _ops
+
+
+def _rel(a, b):
+    return float(np.abs(a - b).max() / np.abs(b).max())
+
+
+def _bf16_round(x):
+    return torch.from_numpy(np.asarray(x, dtype=np.float32)).bfloat16().float().numpy()
+
+
+def _oracle_bf16_mlp(x_pt, x_img, w):
+    """fp64 MLP on bf16-rounded operands with bf16-rounded hidden activations: what the kernel computes."""
+    wq = {k: (_bf16_round(v) if k.endswith("weight") else np.asarray(v, np.float32)) for k, v in w.items()}
+    x = np.concatenate([_bf16_round(x_pt), _bf16_round(x_img)], -1).astype(np.float64)
+    h1 = _bf16_round(np.maximum(x @ wq["mlp.0.weight"].T.astype(np.float64) + wq["mlp.0.bias"], 0)).astype(np.float64)
+    h2 = _bf16_round(np.maximum(h1 @ wq["mlp.2.weight"].T.astype(np.float64) + wq["mlp.2.bias"], 0)).astype(np.float64)
+    return h2 @ wq["mlp.4.weight"].T.astype(np.float64) + wq["mlp.4.bias"]
+
+
+@pytest.mark.parametrize("n", [1, 100, 256, 257, 5000, 40_000])
+def test_mlp_tc_dense(ops, n):
+    gen = torch.Generator().manual_seed(n)
+    x_pt = torch.randn(n, 64, generator=gen)
+    x_img = torch.randn(n, 384, generator=gen)
+    w = synth.make_mlp_weights(3)
+    packed = ops.pack_weights(*[w[k].cuda() for k in W_KEYS])
+    out = ops.mlp_tc(x_pt.cuda(), x_img.cuda(), packed)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    wn = {k: v.numpy() for k, v in w.items()}
+    exact = _oracle_bf16_mlp(x_pt.numpy(), x_img.numpy(), wn)
+    assert _rel(got, exact) < 2e-3, "kernel disagrees with a bf16-operand model of itself"
+    assert _rel(got, O.mlp_forward(x_pt.numpy(), x_img.numpy(), wn)) < BF16_TOL
+
+
+@pytest.mark.parametrize("name", ["fusion_dinov3", "fusion_dinov2", "fusion_hires", "fusion_fp16tok"])
+def test_fused_forward_golden(ops, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name + ".npz"), allow_pickle=False)
+    sw = synth.make_sweeps(int(g["B"]), int(g["V"]), str(g["encoder"]), seed=int(g["seed"]),
+                           tok_dtype=getattr(torch, str(g["tok_dtype"])))
+    w = synth.make_mlp_weights(int(g["seed"]))
+    packed = ops.pack_weights(*[w[k].cuda() for k in W_KEYS])
+    logits, rec = ops.fusion_fwd(sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(),
+                                 sw.image_sizes.float().cuda(), sw.encoder, sw.tokens.cuda(), sw.point_feat.cuda(),
+                                 packed, want_rec=True)
+    torch.cuda.synchronize()
+    assert _rel(logits.cpu().numpy(), g["voxel_scores"]) < BF16_TOL
+    # the records the fused kernel computes inline are the stand-alone projector's, bit for bit
+    ref = ops.project(sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(),
+                      sw.image_sizes.float().cuda(), sw.encoder, want_pix=False, want_depth=False, want_valid=False,
+                      want_rec=True)["rec"]
+    assert torch.equal(rec, ref)
+
+
+def test_dropin_forward_bf16_default(ops, golden_dir, monkeypatch):
+    from utils.fusion_model import FeatureFusionModel
+    monkeypatch.delenv("TDSSF_MLP", raising=False)
+    g = np.load(os.path.join(golden_dir, "fusion_dinov3.npz"), allow_pickle=False)
+    sw = synth.make_sweeps(2, 4096, "dinov3", seed=1)
+
+    class Pcd(torch.nn.Module):
+        def devoxelize(self, s):
+            return s, None
+
+    model = FeatureFusionModel(sw.encoder, Pcd(), device="cuda").cuda()
+    model.load_state_dict(synth.make_mlp_weights(1), strict=True)
+    with torch.no_grad():
+        out = model(sw.tokens, sw.point_feat.cuda(), sw.points.cuda(), None, sw.image_sizes.cuda(), sw.K, sw.Rt)
+    assert _rel(out.cpu().numpy(), g["voxel_scores"]) < BF16_TOL
+    # an optimizer step invalidates the packed bf16 image
+    with torch.no_grad():
+        model.mlp[4].bias.add_(1.0)
+        out2 = model(sw.tokens, sw.point_feat.cuda(), sw.points.cuda(), None, sw.image_sizes.cuda(), sw.K, sw.Rt)
+    assert abs(float((out2 - out).mean()) - 1.0) < 1e-3
+
+
+def test_fused_full_size_config2(ops):
+    """BASELINE config 2 at full size: fused tcgen05 kernel vs the unfused fp32 kernels (already parity-checked)."""
+    sw = synth.make_sweeps(8, 34720, "dinov3", seed=2002)
+    w = synth.make_mlp_weights(2002)
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    pts, K, Rt, hw = sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda()
+    tok, feat = sw.tokens.cuda(), sw.point_feat.cuda()
+    fused = ops.fusion_fwd(pts, K, Rt, hw, sw.encoder, tok, feat, packed)
+    rec = ops.project(pts, K, Rt, hw, sw.encoder, want_pix=False, want_depth=False, want_valid=False, want_rec=True)["rec"]
+    ref = ops.mlp_f32(feat, ops.gather_mean(tok, rec), *wd)
+    assert _rel(fused.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
+    # idempotence: a second launch into the same buffers gives identical bits (no stale TMEM / barrier state)
+    again = ops.fusion_fwd(pts, K, Rt, hw, sw.encoder, tok, feat, packed)
+    assert torch.equal(fused, again)

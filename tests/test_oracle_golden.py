@@ -175,3 +175,21 @@ def test_devox(golden_dir):
     same = ~differ
     assert np.array_equal(out[same], g["out"][same])
     assert differ.mean() < 0.01
+
+
+@pytest.mark.parametrize("name", ["fusion_dinov3", "fusion_dinov2"])
+def test_torch_port_matches_reference(golden_dir, name):
+    """The timed CPU baseline (oracle/torch_port.py) reproduces the reference's outputs."""
+    from oracle import torch_port as T
+    g = _load(golden_dir, name)
+    sw = regen(g)
+    enc = sw.encoder
+    w = synth.make_mlp_weights(int(g["seed"]))
+    with torch.no_grad():
+        out, img, flat, valid, _ = T.fusion_forward(sw.tokens, sw.point_feat, sw.points, sw.image_sizes, sw.K, sw.Rt, w,
+                                                    enc.patch_size, enc.resize_height, enc.resize_width,
+                                                    return_parts=True)
+    assert np.array_equal(valid.numpy(), g["valid"])
+    assert np.array_equal(flat.numpy(), g["flat_idx"])
+    assert np.array_equal(img[:, ::int(g["stride"])].numpy(), g["img_feat_sub"])
+    assert np.abs(out.numpy() - g["voxel_scores"]).max() <= 1e-5 * np.abs(g["voxel_scores"]).max()
