@@ -232,7 +232,7 @@ def test_lidar_encoder_contract(ops):
 
     gen = torch.Generator().manual_seed(3)
     pts = synth.make_points(2, 1500, gen).cuda()
-    pts[1, 700:] = pts[1, :800]  # second sweep has fewer occupied voxels -> padding
+    pts[1, 700:] = pts[1, :800].clone()  # second sweep has fewer occupied voxels -> padding
     enc = LiDARFeatureEncoder({"dataset_params": {"lidar": {"voxel_size": 2.0}}}, backbone=Backbone(), voxelizer=voxelizer).cuda()
     feats, raw, coords, mask = enc(pts)
     assert feats.shape[:2] == raw.shape[:2] == coords.shape[:2] == mask.shape and raw.shape[2] == 4
