@@ -41,8 +41,14 @@ def _newer(src, dst, extra=()):
     return any(os.path.getmtime(s) > t for s in (src, *extra))
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, defines=(), out=None):
+    """defines/out build an experiment variant (e.g. TDSSF_LDMODE=1) into its own object dir and .so."""
+    global OBJ, LIB
     nvcc = nvcc_path()
+    if defines or out:
+        tag = "_".join(d.replace("=", "") for d in defines) or "variant"
+        OBJ = os.path.join(HERE, "build", "variants", tag)
+        LIB = out or os.path.join(OBJ, "libtdssf.so")
     os.makedirs(OBJ, exist_ok=True)
     sources = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
@@ -52,7 +58,7 @@ def build(force=False, verbose=False):
         src = os.path.join(CSRC, f)
         obj = os.path.join(OBJ, f[:-3] + ".o")
         if force or _newer(src, obj, headers):
-            cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
+            cmd = [nvcc, *NVCC_FLAGS, *["-D" + d for d in defines], "-c", src, "-o", obj]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append((f, cmd))
@@ -83,5 +89,7 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--define", action="append", default=[], help="experiment variant, e.g. TDSSF_LDMODE=1")
+    ap.add_argument("--out", default=None)
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose))
+    print(build(force=a.force, verbose=a.verbose, defines=tuple(a.define), out=a.out))

@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "libtdssf.so")
+LIB_PATH = os.environ.get("TDSSF_LIB") or os.path.join(_PKG, "libtdssf.so")  # TDSSF_LIB: experiment variants
 
 OK, EINVAL, ECUDA, ENOSUP, EDEVICE = 0, -1, -2, -3, -4
 F32, F16, BF16 = 0, 1, 2
