@@ -6,12 +6,18 @@
 // shares every B operand: W1 (256x448 bf16 = 224 KB) does not fit one SM's shared memory, split in two
 // N-halves of 112 KB it stays resident for the whole kernel, and so do W2 and W3.
 //
-//   warp 0        TMEM allocation, weight load (cp.async.bulk), MMA issue (leader CTA only)
-//   warps 1-4     epilogue: TMEM -> registers -> bias/ReLU -> bf16 -> TMEM (A operand of the next layer);
-//                 last layer -> logits to HBM
-//   warps 5-20    producers: projection of the tile's points (records in smem), then per 64-channel K slab:
-//                 gather + camera mean from the L2-resident token maps (or dense loads), bf16, written in
-//                 the 128B-swizzled K-major layout the UMMA descriptor expects
+// 16 warps in four warpgroups, register budgets rebalanced with setmaxnreg (launch: 128 per thread):
+//   warps 0-3    epilogue (88 regs): TMEM -> registers -> bias/ReLU -> bf16 -> TMEM (A operand of the next layer);
+//                last layer -> logits to HBM
+//   warp  4      TMEM allocation, weight load (cp.async.bulk), MMA issue (leader CTA only)          (64 regs)
+//   warps 5-6    projectors: lidar->camera->pixel->patch for the tile's points, up to kRecSlots tiles ahead of the
+//                producers; 16-byte camera records go to a shared-memory ring (and to rec_out).  Lane 0 of warp 5
+//                also streams the token maps of the sweeps about to be gathered into L2 (cp.async.bulk.prefetch).
+//   warp  7      idle (keeps the warpgroups aligned)
+//   warps 8-15   producers (176 regs): per 64-channel K slab, gather + camera mean from the L2-resident token maps
+//                (or dense loads), fp32 -> bf16, written in the 128B-swizzled K-major layout the UMMA descriptor
+//                expects.  A thread owns a quarter of four rows; the loads of slab s+1 (first and second camera of
+//                every row, 2 x 64 registers) are in flight while slab s is converted.
 //
 // TMEM (512 columns) holds two 256-column tile buffers; inside a buffer the layer-1 accumulator is
 // overwritten in place by its own bf16 activation (H1), and the layer-2/3 accumulators and H2 reuse
@@ -20,6 +26,7 @@
 // MMA issue order  L1(t+1), L2(t), L3(t)  overlaps the layer-1 epilogue of tile t with the layer-1
 // MMAs of tile t+1.
 #include <algorithm>
+#include <type_traits>
 #include "project.cuh"
 #include "tc_ptx.cuh"
 
@@ -33,9 +40,13 @@ constexpr int kSlabK = 64;                           // K elements per 128-byte 
 constexpr int kSlabs1 = kK1 / kSlabK;                // 7
 constexpr int kSlabs2 = kN1 / kSlabK;                // 4
 constexpr int kStages = 5;
-constexpr int kProducerWarps = 16, kEpiWarps = 4;
-constexpr int kThreads = 32 * (1 + kEpiWarps + kProducerWarps);  // 672
-constexpr int kRowsPerWarp = kTileM / kProducerWarps;            // 8
+constexpr int kEpiWarps = 4, kAuxWarps = 4, kProducerWarps = 8, kHelpWarps = 3;
+constexpr int kMmaWarp = kEpiWarps, kHelpWarp0 = kEpiWarps + 1, kProdWarp0 = kEpiWarps + kAuxWarps;
+constexpr int kThreads = 32 * (kEpiWarps + kAuxWarps + kProducerWarps);  // 512
+constexpr int kRowsPerWarp = kTileM / kProducerWarps;                    // 16
+constexpr int kSteps = kRowsPerWarp / 4;                                 // 4 rows per quarter-warp
+constexpr int kRecSlots = 3;                                             // tiles of row descriptors in flight
+constexpr int kRegsEpi = 88, kRegsAux = 128, kRegsProd = 144;            // 128*(88+128) + 256*144 = 64512
 
 // per-CTA shared-memory image (bytes)
 constexpr int kW1Slab = (kN1 / 2) * 128;   // 128 rows x 128 B = 16 KB
@@ -50,12 +61,13 @@ constexpr int kOffRing = kWeightBytes;                      // 1024-aligned
 constexpr int kASlab = kTileM * 128;                        // 16 KB
 constexpr int kOffBias = kOffRing + kStages * kASlab;       // 215040
 constexpr int kOffRec = kOffBias + ((kBiasFloats * 4 + 15) & ~15);
-constexpr int kOffBar = kOffRec + 2 * kTileM * 32;     // [warp][2 tiles][8 rows] x 8 slot words
-constexpr int kNumBars = 2 * kStages + 2 + 6 * 2;           // a_full, a_empty, w_full, peer_w, 6 per-buffer kinds x 2
+constexpr int kOffBar = kOffRec + kRecSlots * kTileM * 8;   // row sources: [slot][128 rows] x 8 B (a pointer)
+constexpr int kNumBars = 2 * kStages + 2 + 6 * 2 + 2 * kRecSlots;
 constexpr int kOffTmemPtr = kOffBar + kNumBars * 8;
 constexpr int kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget exceeded");
 static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0, "slab alignment");
+static_assert(128 * (kRegsEpi + kRegsAux) + 256 * kRegsProd <= 65536, "register budget");
 
 constexpr size_t kPackBytes = 2 * (size_t)kWeightBytes + kBiasFloats * 4 + 64;
 
@@ -71,6 +83,8 @@ enum {
   kBarH1Full = kBarAcc3Full + 2,       // [2] leader: 2*kEpiWarps arrivals
   kBarH2Full = kBarH1Full + 2,         // [2]
   kBarAccFree = kBarH2Full + 2,        // [2]
+  kBarRecFull = kBarAccFree + 2,       // [kRecSlots] kHelpWarps arrivals
+  kBarRecEmpty = kBarRecFull + kRecSlots,  // [kRecSlots] kProducerWarps arrivals
 };
 
 struct Params {
@@ -87,6 +101,8 @@ struct Params {
   float* logits;               // [N,16]
   int64_t N;
   int n_pairs;                 // number of 256-row tile pairs
+  const void* zeros;           // >= 4 KB of zeros (source of rows without a camera / beyond N)
+  void* scratch;               // [gridDim][kRecSlots][128] token rows: means of multi-camera rows
   unsigned int* debug;         // optional: [0] = timeout code
 };
 
@@ -106,17 +122,16 @@ struct Params {
 __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* debug, int code) {
   if (ptx::mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
-#ifdef TDSSF_PROFILE
-  struct Acc { unsigned int* d; int c; long long t; __device__ ~Acc() { PROF_ADD(d, c, t); } } acc_{debug, code, t0};
-#endif
   while (!ptx::mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > 4000000000LL) {  // ~2 s: a protocol bug, never a legitimate wait
       if (debug) atomicExch(debug, (unsigned)code | 0x80000000u);
       __trap();
     }
   }
+#ifdef TDSSF_PROFILE
+  PROF_ADD(debug, code, t0);
+#endif
 }
-
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -128,25 +143,14 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // fully coalesced 128-byte requests: lane ql takes channels [4ql,4ql+4) and [32+4ql,32+4ql+4).  16-bit sources
 // (128 B) are one request: lane ql takes channels [8ql,8ql+8).  Loads return raw bits; conversion is deferred to the
 // consumer so that the request stays in flight.
-#ifndef TDSSF_LDMODE
-#define TDSSF_LDMODE 0  // 0: ld.global.nc   1: ld.global.cg (L2 only)   2: ld.global.nc.L1::no_allocate
-#endif
-__device__ __forceinline__ uint4 ldg16(const void* p) {
-#if TDSSF_LDMODE == 1
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// coherent 16-byte load: the scratch rows of multi-camera points are written by this CTA during the kernel
+__device__ __forceinline__ uint4 ldg16c(const void* p) {
   uint4 r;
-  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
-#elif TDSSF_LDMODE == 2
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-  return r;
-#else
-  return __ldg(reinterpret_cast<const uint4*>(p));
-#endif
 }
 struct Raw8 { uint4 lo, hi; };
-__device__ __forceinline__ Raw8 raw8_zero() { Raw8 r; r.lo = make_uint4(0, 0, 0, 0); r.hi = r.lo; return r; }
-// piece = start of the row's 64-channel piece
 __device__ __forceinline__ Raw8 raw8_load_f32(const float* piece, int ql) {
   Raw8 r;
   r.lo = ldg16(piece + ql * 4);
@@ -160,15 +164,13 @@ __device__ __forceinline__ void raw8_f32_to_f8(const Raw8& q, float (&f)[8]) {
 template <typename T> struct TokRaw;
 template <> struct TokRaw<float> {
   static constexpr bool kSplit = true;
-  __device__ static Raw8 load(const float* piece, int ql) { return raw8_load_f32(piece, ql); }
-  __device__ static void to_f8(const Raw8& q, float (&f)[8]) { raw8_f32_to_f8(q, f); }
+  __device__ static __forceinline__ void load(Raw8& r, const float* piece, int ql) { r = raw8_load_f32(piece, ql); }
+  __device__ static __forceinline__ void to_f8(const Raw8& q, float (&f)[8]) { raw8_f32_to_f8(q, f); }
 };
 template <> struct TokRaw<__half> {
   static constexpr bool kSplit = false;
-  __device__ static Raw8 load(const __half* piece, int ql) {
-    Raw8 r; r.lo = ldg16(piece + ql * 8); r.hi = make_uint4(0, 0, 0, 0); return r;
-  }
-  __device__ static void to_f8(const Raw8& q, float (&f)[8]) {
+  __device__ static __forceinline__ void load(Raw8& r, const __half* piece, int ql) { r.lo = ldg16(piece + ql * 8); }
+  __device__ static __forceinline__ void to_f8(const Raw8& q, float (&f)[8]) {
     uint32_t w[4] = {q.lo.x, q.lo.y, q.lo.z, q.lo.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) { const float2 a = __half22float2(*reinterpret_cast<__half2*>(&w[i])); f[2 * i] = a.x; f[2 * i + 1] = a.y; }
@@ -176,10 +178,8 @@ template <> struct TokRaw<__half> {
 };
 template <> struct TokRaw<__nv_bfloat16> {
   static constexpr bool kSplit = false;
-  __device__ static Raw8 load(const __nv_bfloat16* piece, int ql) {
-    Raw8 r; r.lo = ldg16(piece + ql * 8); r.hi = make_uint4(0, 0, 0, 0); return r;
-  }
-  __device__ static void to_f8(const Raw8& q, float (&f)[8]) {
+  __device__ static __forceinline__ void load(Raw8& r, const __nv_bfloat16* piece, int ql) { r.lo = ldg16(piece + ql * 8); }
+  __device__ static __forceinline__ void to_f8(const Raw8& q, float (&f)[8]) {
     uint32_t w[4] = {q.lo.x, q.lo.y, q.lo.z, q.lo.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) { const float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w[i])); f[2 * i] = a.x; f[2 * i + 1] = a.y; }
@@ -199,24 +199,11 @@ __device__ __forceinline__ void store_row8(uint8_t* slab, int r, int ql, const f
   }
 }
 
-// cameras beyond the preloaded ones (rare): sequential loads in camera order, straight from the slot words
-template <typename TokT>
-__device__ __noinline__ void gather_rest(const uint32_t* sl, int covered, const TokT* tokens, int NC, int M, int ch0,
-                                         int ql, float (&acc)[8]) {
-  const uint32_t tok_row_base = sl[6] * (uint32_t)(NC * M);
-  int k = 0;
-  for (int c = 0; c < TDSSF_MAX_CAMS; ++c) {
-    const uint32_t v = sl[c];
-    if (v >> 31) {
-      if (k >= covered) {
-        float f[8];
-        TokRaw<TokT>::to_f8(TokRaw<TokT>::load(tokens + (int64_t)(tok_row_base + c * M + (v & 0xffffu)) * kCi + ch0, ql), f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
-      }
-      k++;
-    }
-  }
+// Row of the warp's 16 that quarter-warp q handles in step st.  Within one step the four quarters write rows whose
+// swizzle phases (r & 7) are {a, a+4, a+1, a+5}: two of them land in the low 64 bytes of the 128-byte bank window and
+// two in the high 64 bytes, so an 8-byte-per-lane store is the minimum two wavefronts.
+__device__ __forceinline__ int row_of(int st, int q) {
+  return ((q & 1) << 2) | (q >> 1) | ((st & 1) << 1) | ((st >> 1) << 3);
 }
 
 // kGather: image channels come from the token maps through the records; else from p.x_img
@@ -232,6 +219,9 @@ fused_mlp_kernel(const Params p) {
   const bool leader = rank == 0;
   const int n_iters = (p.n_pairs - (int)ptx::cluster_id_x() + (int)ptx::num_clusters_x() - 1) / (int)ptx::num_clusters_x();
   auto bar = [&](int i) { return sbase + kOffBar + 8 * i; };
+  auto tile_row0 = [&](int it) {
+    return (((int64_t)ptx::cluster_id_x() + (int64_t)it * ptx::num_clusters_x()) * 2 + rank) * kTileM;
+  };
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + kOffTmemPtr);
 
@@ -251,13 +241,17 @@ fused_mlp_kernel(const Params p) {
       ptx::mbar_init(bar(kBarH2Full + b), 2 * kEpiWarps);
       ptx::mbar_init(bar(kBarAccFree + b), 2 * kEpiWarps);
     }
+    for (int s = 0; s < kRecSlots; ++s) {
+      ptx::mbar_init(bar(kBarRecFull + s), kHelpWarps);
+      ptx::mbar_init(bar(kBarRecEmpty + s), kProducerWarps);
+    }
     ptx::fence_mbar_init();
   }
   {  // biases (shared by both ranks) live after the two weight images
     const float* gb = reinterpret_cast<const float*>(p.packed + 2 * (size_t)kWeightBytes);
     for (int i = threadIdx.x; i < kBiasFloats; i += kThreads) s_bias[i] = __ldg(gb + i);
   }
-  if (warp == 0) {
+  if (warp == kMmaWarp) {
     ptx::tmem_alloc_2cta(sbase + kOffTmemPtr, 512);
     ptx::tmem_relinquish_2cta();
   }
@@ -267,88 +261,21 @@ fused_mlp_kernel(const Params p) {
   ptx::tc_fence_after();
   const uint32_t tmem = *s_tmem;
 
-  if (warp == 0) {
-    // =============================== weights + MMA issue ==========================================
-    if (lane == 0) {
-      const uint8_t* src = p.packed + (size_t)rank * kWeightBytes;
-      ptx::mbar_expect_tx(bar(kBarWFull), kWeightBytes);
-      for (int off = 0; off < kWeightBytes; off += 16384) {
-        const int n = min(16384, kWeightBytes - off);
-        ptx::bulk_g2s(sbase + kOffW1 + off, src + off, n, bar(kBarWFull));
-      }
-    }
-    if (leader && lane == 0 && n_iters > 0) {
-      // B operands are read from both CTAs' shared memory: wait for our image and for the peer's
-      wait_bar(bar(kBarWFull), 0, p.debug, 1);
-      wait_bar(bar(kBarPeerW), 0, p.debug, 11);
-      constexpr uint32_t kI1 = ptx::idesc_bf16(256, kN1), kI2 = ptx::idesc_bf16(256, kN2), kI3 = ptx::idesc_bf16(256, kN3);
-      uint32_t g = 0;  // global slab counter
-      auto issue_l1 = [&](int it) {
-        const uint32_t buf = it & 1;
-        if (it >= 2) wait_bar(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, p.debug, 2);
-        ptx::tc_fence_after();
-        for (int s = 0; s < kSlabs1; ++s, ++g) {
-          const uint32_t stage = g % kStages, par = (g / kStages) & 1;
-          wait_bar(bar(kBarAFull + stage), par, p.debug, 3);
-          ptx::tc_fence_after();
-#pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t ad = ptx::smem_desc_sw128(sbase + kOffRing + stage * kASlab + kk * 32);
-            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW1 + s * kW1Slab + kk * 32);
-            ptx::umma_ss_2cta(tmem + buf * 256, ad, bd, kI1, (s | kk) != 0);
-          }
-          ptx::umma_commit_2cta(bar(kBarAEmpty + stage), 3);
-        }
-        ptx::umma_commit_2cta(bar(kBarAcc1Full + buf), 3);
-      };
-      PROF_T0(t25);
-      issue_l1(0);
-      for (int it = 0; it < n_iters; ++it) {
-        const uint32_t buf = it & 1, par = (it >> 1) & 1;
-        if (it + 1 < n_iters) issue_l1(it + 1);
-        // layer 2: A = H1 (TMEM cols [0,128) of the buffer), B = W2
-        wait_bar(bar(kBarH1Full + buf), par, p.debug, 4);
-        ptx::tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < kN1 / 16; ++k) {
-          const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
-          ptx::umma_ts_2cta(tmem + buf * 256 + 128, tmem + buf * 256 + k * 8, bd, kI2, k != 0);
-        }
-        ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
-        // layer 3: A = H2 (cols [192,224)), B = W3
-        wait_bar(bar(kBarH2Full + buf), par, p.debug, 5);
-        ptx::tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < kN2 / 16; ++k) {
-          const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
-          ptx::umma_ts_2cta(tmem + buf * 256 + 224, tmem + buf * 256 + 192 + k * 8, bd, kI3, k != 0);
-        }
-        ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
-      }
-      PROF_ADD(p.debug, 25, t25);
-    }
-    if (!leader && lane == 0) {
-      wait_bar(bar(kBarWFull), 0, p.debug, 6);
-      ptx::mbar_arrive_cluster(ptx::mapa(bar(kBarPeerW), 0));
-    }
-    __syncwarp();
-  } else if (warp <= kEpiWarps) {
+  if (warp < kEpiWarps) {
     // =============================== epilogue ======================================================
-    const uint32_t lane_base = (uint32_t)(warp & 3) * 32;
+    ptx::setmaxnreg_dec<kRegsEpi>();
+    const uint32_t lane_base = (uint32_t)warp * 32;
     const uint32_t tlane = tmem + (lane_base << 16);
     const int row_in_tile = (int)lane_base + lane;
     const uint32_t leader_h1 = ptx::mapa(bar(kBarH1Full), 0), leader_h2 = ptx::mapa(bar(kBarH2Full), 0),
                    leader_free = ptx::mapa(bar(kBarAccFree), 0);
-    PROF_T0(t26);
     for (int it = 0; it < n_iters; ++it) {
       const uint32_t buf = it & 1, par = (it >> 1) & 1;
-      const int64_t pair = (int64_t)ptx::cluster_id_x() + (int64_t)it * ptx::num_clusters_x();
-      const int64_t row = (pair * 2 + rank) * kTileM + row_in_tile;
+      const int64_t row = tile_row0(it) + row_in_tile;
       const uint32_t tb = tlane + buf * 256;
       // ---- layer 1: acc1 -> relu(+b1) -> bf16 H1, in place --------------------------------------
       wait_bar(bar(kBarAcc1Full + buf), par, p.debug, 7);
       ptx::tc_fence_after();
-      PROF_T0(t27);
 #pragma unroll 1
       for (int q = 0; q < kN1 / 32; ++q) {
         uint32_t v[32], h[16];
@@ -367,7 +294,6 @@ fused_mlp_kernel(const Params p) {
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(leader_h1 + 8 * buf);
       __syncwarp();
-      PROF_ADD(p.debug, 27, t27);
       // ---- layer 2: acc2 -> relu(+b2) -> bf16 H2 --------------------------------------------------
       wait_bar(bar(kBarAcc2Full + buf), par, p.debug, 8);
       ptx::tc_fence_after();
@@ -411,268 +337,346 @@ fused_mlp_kernel(const Params p) {
         }
       }
     }
-    PROF_ADD(p.debug, 26, t26);
-  } else {
-    // =============================== producers =====================================================
-    // Per tile: (1) every (row, camera) pair is projected by its own thread into a slot word
-    // "valid<<31 | patch" (done one tile ahead, while gather loads are in flight); (2) each warp compacts
-    // the slots of its 8 rows into "first / second valid token row"; (3) per 64-channel K slab all loads of
-    // the warp's rows are issued before any is consumed, and the next slab's loads are issued before the
-    // current slab is converted (two register sets) so that ~2 slabs of L2 requests stay in flight per SM.
-    const int pw = warp - 1 - kEpiWarps;                  // 0..15
-    const int ptid = threadIdx.x - 32 * (1 + kEpiWarps);  // 0..511
-    const int quarter = lane >> 3, ql = lane & 7;
-    const uint32_t leader_full0 = ptx::mapa(bar(kBarAFull), 0);
-    uint32_t* s_slot = reinterpret_cast<uint32_t*>(smem + kOffRec);  // [16 warps][2 tiles][8 rows][8]
-    auto tile_row0 = [&](int it) {
-      return (((int64_t)ptx::cluster_id_x() + (int64_t)it * ptx::num_clusters_x()) * 2 + rank) * kTileM;
-    };
-
-    // warp-private slot words: [warp][2 tiles][8 rows][8] — each warp projects, compacts and gathers its own 8 rows,
-    // so the producers never wait for one another
-    auto slots_of = [&](int it) { return s_slot + ((pw * 2 + (it & 1)) * kRowsPerWarp) * 8; };
-    auto fill_slots = [&](int it) {
-      uint32_t* slots = slots_of(it);
-      const int64_t row0 = tile_row0(it) + pw * kRowsPerWarp;
-      if (p.rec_in) {
-        if (lane < kRowsPerWarp) {
-          const int64_t row = row0 + lane;
-          uint4 r = make_uint4(0, 0, 0, 0);
-          uint32_t b = 0;
-          if (row < p.N) {
-            r = __ldg(reinterpret_cast<const uint4*>(p.rec_in) + row);
-            b = (uint32_t)(row / p.V);
-          }
-          const uint32_t pk[3] = {r.x, r.y, r.z};
-#pragma unroll
-          for (int c = 0; c < TDSSF_MAX_CAMS; ++c)
-            slots[lane * 8 + c] = ((pk[c >> 1] >> ((c & 1) * 16)) & 0xffffu) | (((r.w >> c) & 1u) << 31);
-          slots[lane * 8 + 6] = b;
+  } else if (warp < kProdWarp0) {
+    if (warp == kMmaWarp) {
+      // =============================== weights + MMA issue ==========================================
+      if (lane == 0) {
+        const uint8_t* src = p.packed + (size_t)rank * kWeightBytes;
+        ptx::mbar_expect_tx(bar(kBarWFull), kWeightBytes);
+        for (int off = 0; off < kWeightBytes; off += 16384) {
+          const int n = min(16384, kWeightBytes - off);
+          ptx::bulk_g2s(sbase + kOffW1 + off, src + off, n, bar(kBarWFull));
         }
-        return;
       }
+      if (leader && lane == 0 && n_iters > 0) {
+        // B operands are read from both CTAs' shared memory: wait for our image and for the peer's
+        wait_bar(bar(kBarWFull), 0, p.debug, 1);
+        wait_bar(bar(kBarPeerW), 0, p.debug, 11);
+        constexpr uint32_t kI1 = ptx::idesc_bf16(256, kN1), kI2 = ptx::idesc_bf16(256, kN2), kI3 = ptx::idesc_bf16(256, kN3);
+        uint32_t stage = 0, phase = 0;  // A ring cursor
+        auto issue_l1 = [&](int it) {
+          const uint32_t buf = it & 1;
+          if (it >= 2) wait_bar(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, p.debug, 2);
+          ptx::tc_fence_after();
+#pragma unroll 1
+          for (int s = 0; s < kSlabs1; ++s) {
+            wait_bar(bar(kBarAFull + stage), phase, p.debug, 3);
+            ptx::tc_fence_after();
 #pragma unroll
-      for (int jj = 0; jj < 2; ++jj) {
-        const int j = lane + 32 * jj;  // 48 (row, camera) pairs over 32 lanes
-        if (j < kRowsPerWarp * TDSSF_MAX_CAMS) {
-          const int cam = j >> 3, r = j & (kRowsPerWarp - 1);
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t ad = ptx::smem_desc_sw128(sbase + kOffRing + stage * kASlab + kk * 32);
+              const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW1 + s * kW1Slab + kk * 32);
+              ptx::umma_ss_2cta(tmem + buf * 256, ad, bd, kI1, (s | kk) != 0);
+            }
+            ptx::umma_commit_2cta(bar(kBarAEmpty + stage), 3);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+          ptx::umma_commit_2cta(bar(kBarAcc1Full + buf), 3);
+        };
+        issue_l1(0);
+        for (int it = 0; it < n_iters; ++it) {
+          const uint32_t buf = it & 1, par = (it >> 1) & 1;
+          if (it + 1 < n_iters) issue_l1(it + 1);
+          // layer 2: A = H1 (TMEM cols [0,128) of the buffer), B = W2
+          wait_bar(bar(kBarH1Full + buf), par, p.debug, 4);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < kN1 / 16; ++k) {
+            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
+            ptx::umma_ts_2cta(tmem + buf * 256 + 128, tmem + buf * 256 + k * 8, bd, kI2, k != 0);
+          }
+          ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
+          // layer 3: A = H2 (cols [192,224)), B = W3
+          wait_bar(bar(kBarH2Full + buf), par, p.debug, 5);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < kN2 / 16; ++k) {
+            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
+            ptx::umma_ts_2cta(tmem + buf * 256 + 224, tmem + buf * 256 + 192 + k * 8, bd, kI3, k != 0);
+          }
+          ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
+        }
+      }
+      if (!leader && lane == 0) {
+        wait_bar(bar(kBarWFull), 0, p.debug, 6);
+        ptx::mbar_arrive_cluster(ptx::mapa(bar(kBarPeerW), 0));
+      }
+      __syncwarp();
+    } else if (kGather) {
+      // =============================== helpers: projection + multi-camera rows ========================
+      // One lane per point, the cameras in sequence (calibration through the read-only L1 path: every lane of the
+      // warp reads the same 21 floats unless the tile straddles two sweeps).  The result per row is ONE source
+      // pointer for the producers: the token row of its camera, a row of zeros (no camera), or - for the ~6 % of
+      // rows seen by several cameras - a scratch row in which the warp has written the camera-order sum divided by
+      // the count (utils/fusion_model.py:195-201).  Runs up to kRecSlots tiles ahead of the producers.
+      const int hw = warp - kHelpWarp0;  // 0..2
+      const char** s_src = reinterpret_cast<const char**>(smem + kOffRec);
+      constexpr int kRowBytes = kCi * (int)sizeof(TokT);
+      constexpr int kChunks = kRowBytes / 16;  // 96 (fp32) or 48 (16-bit)
+      const char* const tok = reinterpret_cast<const char*>(p.tokens);
+      const int64_t tok_sweep_bytes = (int64_t)p.NC * p.M * kRowBytes;
+      const int n_sweeps = (int)((p.N + p.V - 1) / p.V);
+      const int pf_ahead = tok_sweep_bytes <= (32 << 20) ? 2 : 1;
+      int pf_next = 0;  // first sweep whose token map has not been requested yet (lane 0 of helper 0)
+      for (int it = 0; it < n_iters; ++it) {
+        const int slot = it % kRecSlots;
+        const int64_t row0 = tile_row0(it);
+        if (it >= kRecSlots) wait_bar(bar(kBarRecEmpty + slot), ((it / kRecSlots) - 1) & 1, p.debug, 13);
+        if (hw == 0 && lane == 0) {
+          // L2 prefetch (TMA bulk prefetch, no registers, no completion tracking): the gather visits the token rows
+          // of a sweep in random order, slab by slab; streaming the whole map of the sweeps about to be processed
+          // into L2 sequentially (each CTA every gridDim-th 16 KB chunk) keeps the gather loads L2 hits.
+          const int want = min(n_sweeps, (int)(min((long long)(row0 + kTileM - 1), (long long)(p.N - 1)) / p.V) + 1 + pf_ahead);
+          for (; pf_next < want; ++pf_next) {
+            const char* base = tok + (int64_t)pf_next * tok_sweep_bytes;
+            for (int64_t off = (int64_t)blockIdx.x * 16384; off < tok_sweep_bytes; off += (int64_t)gridDim.x * 16384)
+              ptx::prefetch_l2(base + off, (uint32_t)min((long long)16384, (long long)(tok_sweep_bytes - off)));
+          }
+          const int64_t r2 = tile_row0(it + 2);  // point features two tiles ahead: one contiguous block
+          if (it + 2 < n_iters && r2 < p.N)
+            ptx::prefetch_l2(p.x_pt + r2 * kCp, (uint32_t)(min((long long)kTileM, (long long)(p.N - r2)) * kCp * 4));
+        }
+        char* const scratch = reinterpret_cast<char*>(p.scratch) + ((int64_t)blockIdx.x * kRecSlots + slot) * kTileM * kRowBytes;
+#pragma unroll 1
+        for (int g = 0; g < kTileM / 32; ++g) {
+          if ((g + it) % kHelpWarps != hw) continue;  // four 32-row groups over three warps, rotating
+          const int r = g * 32 + lane;
           const int64_t row = row0 + r;
-          uint32_t val = 0, b = 0;
+          uint32_t idx[TDSSF_MAX_CAMS] = {0u, 0u, 0u, 0u, 0u, 0u}, cnt = 0;  // token rows of the valid cameras, camera order
           if (row < p.N) {
-            b = (uint32_t)(row / p.V);
-            if (cam < p.NC) {
+            const uint32_t b = (uint32_t)(row / p.V);
+            const uint32_t tok_base = b * (uint32_t)(p.NC * p.M);
+            auto push = [&](uint32_t cam, uint32_t patch) {
+              const uint32_t t = tok_base + cam * (uint32_t)p.M + patch;
+#pragma unroll
+              for (int k = 0; k < TDSSF_MAX_CAMS; ++k) if ((uint32_t)k == cnt) idx[k] = t;
+              ++cnt;
+            };
+            if (p.rec_in) {
+              const uint4 rec = __ldg(reinterpret_cast<const uint4*>(p.rec_in) + row);
+              const uint32_t pk[3] = {rec.x, rec.y, rec.z};
+#pragma unroll
+              for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam)
+                if ((rec.w >> cam) & 1u) push((uint32_t)cam, (pk[cam >> 1] >> ((cam & 1) * 16)) & 0xffffu);
+            } else {
               const int v = (int)(row - (int64_t)b * p.V);
               const float* q = p.xyz + b * p.sweep_stride + v * p.point_stride;
               const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
               const SweepGeom geo = make_geom(__ldg(p.img_hw + 2 * b), __ldg(p.img_hw + 2 * b + 1), p.resize_h, p.resize_w, p.patch);
-              CamCalib cal;
-              const float* rt = p.Rt + ((int64_t)b * p.NC + cam) * 16;
-              const float* kk = p.K + ((int64_t)b * p.NC + cam) * 9;
+              uint32_t pk[3] = {0u, 0u, 0u}, mask = 0;
+#pragma unroll 1
+              for (int cam = 0; cam < p.NC; ++cam) {
+                CamCalib cal;
+                const float* rt = p.Rt + ((int64_t)b * p.NC + cam) * 16;
+                const float* kk = p.K + ((int64_t)b * p.NC + cam) * 9;
 #pragma unroll
-              for (int i = 0; i < 12; ++i) (&cal.r[0][0])[i] = __ldg(rt + i);
+                for (int i = 0; i < 12; ++i) (&cal.r[0][0])[i] = __ldg(rt + i);
 #pragma unroll
-              for (int i = 0; i < 9; ++i) (&cal.k[0][0])[i] = __ldg(kk + i);
-              const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
-              val = (uint32_t)patch_index(geo, pr.u, pr.v) | (pr.valid ? 0x80000000u : 0u);
+                for (int i = 0; i < 9; ++i) (&cal.k[0][0])[i] = __ldg(kk + i);
+                const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
+                const uint32_t f = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
+                const uint32_t sh = (uint32_t)(cam & 1) * 16u;
+                if ((cam >> 1) == 0) pk[0] |= f << sh; else if ((cam >> 1) == 1) pk[1] |= f << sh; else pk[2] |= f << sh;
+                if (pr.valid) { mask |= 1u << cam; push((uint32_t)cam, f); }
+              }
+              if (p.rec_out) reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pk[0], pk[1], pk[2], mask | (cnt << 8));
             }
           }
-          slots[r * 8 + cam] = val;
-          if (cam == 0) slots[r * 8 + 6] = b;
-        }
-      }
-    };
-
-    // L2 prefetch (TMA bulk prefetch, no registers, no completion tracking).  The gather visits every token row six
-    // times, slab by slab, so demand misses would hit DRAM with scattered 256-byte reads at full DRAM latency; instead
-    // the whole token map of the sweeps about to be processed is streamed into L2 sequentially, each CTA taking every
-    // gridDim-th 16 KB chunk, and the next tiles' point features / points are prefetched as they are contiguous.
-    const int64_t tok_sweep_bytes = (int64_t)p.NC * p.M * kCi * (int64_t)sizeof(TokT);
-    const int pf_ahead = tok_sweep_bytes <= (32 << 20) ? 2 : 1;
-    int pf_next = 0;  // first sweep whose token map has not been requested yet (meaningful in thread ptid == 0)
-    auto prefetch_for_tile = [&](int it) {
-      if (ptid != 0) return;
-      const int64_t row0 = tile_row0(it);
-      if (kGather) {
-        const int n_sweeps = (int)((p.N + p.V - 1) / p.V);
-        const int want = min(n_sweeps, (int)(min((long long)(row0 + kTileM - 1), (long long)(p.N - 1)) / p.V) + 1 + pf_ahead);
-        for (; pf_next < want; ++pf_next) {
-          const uint8_t* base = reinterpret_cast<const uint8_t*>(p.tokens) + (int64_t)pf_next * tok_sweep_bytes;
-          for (int64_t off = (int64_t)blockIdx.x * 16384; off < tok_sweep_bytes; off += (int64_t)gridDim.x * 16384)
-            ptx::prefetch_l2(base + off, (uint32_t)min((long long)16384, (long long)(tok_sweep_bytes - off)));
-        }
-      }
-      const int64_t r2 = tile_row0(it + 2);  // point features (and points) two tiles ahead: contiguous blocks
-      if (it + 2 < n_iters && r2 < p.N) {
-        const int64_t rows = min((long long)kTileM, (long long)(p.N - r2));
-        ptx::prefetch_l2(p.x_pt + r2 * kCp, (uint32_t)(rows * kCp * 4));
-        if (!kGather) {
-          ptx::prefetch_l2(p.x_img + r2 * kCi, (uint32_t)(rows * kCi * 4));
-        } else if (!p.rec_in && r2 / p.V == (r2 + rows - 1) / p.V && (p.point_stride & 3) == 0) {
-          const int64_t b = r2 / p.V;
-          const float* q = p.xyz + b * p.sweep_stride + (r2 - b * p.V) * p.point_stride;
-          if ((reinterpret_cast<uintptr_t>(q) & 15) == 0) ptx::prefetch_l2(q, (uint32_t)(rows * p.point_stride * 4));
-        }
-      }
-    };
-
-    // quarter-warp q owns row pw*8 + step*4 + q of the tile; lane ql of the quarter owns 8 channels of the slab
-    constexpr int kSteps = kRowsPerWarp / 4;  // 2
-    struct TileRec {
-      uint32_t base0[kSteps];  // token row (sweep, camera, patch) of the first valid camera
-      uint32_t cn[kSteps];     // number of valid cameras
-      uint32_t ovb;            // token row of the second camera of step `ovs`
-      int ovs;                 // the step (if any) whose row has a second camera preloaded, else -1
-    };
-
-    // compaction of the slots of tile `it`: lane j < 8 owns row pw*8 + j, results are shuffled to the quarters
-    auto compact = [&](int it, TileRec& R) {
-      const uint32_t* slots = slots_of(it);
-      const int64_t row0 = tile_row0(it);
-      uint32_t c_i0 = 0, c_i1 = 0, c_cnt = 0;
-      if (lane < kRowsPerWarp) {
-        const int r = pw * kRowsPerWarp + lane;
-        const uint4 a = *reinterpret_cast<const uint4*>(slots + lane * 8);
-        const uint4 bq = *reinterpret_cast<const uint4*>(slots + lane * 8 + 4);
-        const uint32_t sl[6] = {a.x, a.y, a.z, a.w, bq.x, bq.y};
-        const uint32_t tok_row_base = bq.z * (uint32_t)(p.NC * p.M);
-        uint32_t mask = 0;
+          s_src[slot * kTileM + r] = cnt == 0 ? reinterpret_cast<const char*>(p.zeros)
+                                   : cnt == 1 ? tok + (int64_t)idx[0] * kRowBytes
+                                              : scratch + (int64_t)r * kRowBytes;
+          // rows with several cameras: the whole warp sums one row at a time, 16 bytes per lane and pass
+          uint32_t multi = __ballot_sync(0xffffffffu, cnt >= 2);
+          while (multi) {
+            const int src = __ffs(multi) - 1;
+            multi &= multi - 1;
+            const uint32_t cn = __shfl_sync(0xffffffffu, cnt, src);
+            uint32_t t[TDSSF_MAX_CAMS];
 #pragma unroll
-        for (int c = 0; c < TDSSF_MAX_CAMS; ++c) {
-          if (sl[c] >> 31) {
-            const uint32_t idx = tok_row_base + (uint32_t)c * p.M + (sl[c] & 0xffffu);
-            if (c_cnt == 0) c_i0 = idx;
-            else if (c_cnt == 1) c_i1 = idx;
-            c_cnt++;
-            mask |= 1u << c;
-          }
-        }
-        if (p.rec_out && !p.rec_in && row0 + r < p.N)
-          reinterpret_cast<uint4*>(p.rec_out)[row0 + r] =
-              make_uint4((sl[0] & 0xffffu) | (sl[1] << 16), (sl[2] & 0xffffu) | (sl[3] << 16),
-                         (sl[4] & 0xffffu) | (sl[5] << 16), mask | (c_cnt << 8));
-      }
-      R.ovs = -1;
-      R.ovb = 0;
+            for (int k = 0; k < TDSSF_MAX_CAMS; ++k) t[k] = __shfl_sync(0xffffffffu, idx[k], src);
+            char* dst = scratch + (int64_t)(g * 32 + src) * kRowBytes;
+            const float den = (float)cn;
 #pragma unroll
-      for (int step = 0; step < kSteps; ++step) {
-        const int src = step * 4 + quarter;
-        R.base0[step] = __shfl_sync(0xffffffffu, c_i0, src);
-        const uint32_t i1 = __shfl_sync(0xffffffffu, c_i1, src);
-        R.cn[step] = __shfl_sync(0xffffffffu, c_cnt, src);
-        if (R.cn[step] >= 2 && R.ovs < 0) { R.ovs = step; R.ovb = i1; }
-      }
-    };
-
-    auto tok_piece = [&](uint32_t tok_row, int s) {
-      return reinterpret_cast<const TokT*>(p.tokens) + (int64_t)tok_row * kCi + (s - 1) * kSlabK;
-    };
-    // loads of slab s of the tile whose first row is row0 (records R); nothing is consumed here
-    auto issue = [&](int64_t row0, const TileRec& R, int s, Raw8 (&t)[kSteps], Raw8& u) {
+            for (int c0 = 0; c0 < kChunks; c0 += 32) {
+              const int c = c0 + lane;
+              if (c < kChunks) {
+                Raw8 q0, q1;
+                q0.lo = ldg16(tok + (int64_t)t[0] * kRowBytes + c * 16);
+                q1.lo = ldg16(tok + (int64_t)t[1] * kRowBytes + c * 16);
+                float acc[8], f[8];
+                constexpr int kE = 16 / (int)sizeof(TokT);  // elements per chunk: 4 or 8
+                if (sizeof(TokT) == 4) {
+                  acc[0] = __uint_as_float(q0.lo.x); acc[1] = __uint_as_float(q0.lo.y); acc[2] = __uint_as_float(q0.lo.z); acc[3] = __uint_as_float(q0.lo.w);
+                  f[0] = __uint_as_float(q1.lo.x); f[1] = __uint_as_float(q1.lo.y); f[2] = __uint_as_float(q1.lo.z); f[3] = __uint_as_float(q1.lo.w);
+                } else {
+                  TokRaw<TokT>::to_f8(q0, acc);
+                  TokRaw<TokT>::to_f8(q1, f);
+                }
 #pragma unroll
-      for (int step = 0; step < kSteps; ++step) {
-        const int64_t row = row0 + pw * kRowsPerWarp + step * 4 + quarter;
-        t[step] = raw8_zero();
-        if (s == 0) {
-          if (row < p.N) t[step] = raw8_load_f32(p.x_pt + row * kCp, ql);
-        } else if (!kGather) {
-          if (row < p.N) t[step] = raw8_load_f32(p.x_img + row * kCi + (s - 1) * kSlabK, ql);
-        } else if (R.cn[step] >= 1) {
-          t[step] = TokRaw<TokT>::load(tok_piece(R.base0[step], s), ql);
-        }
-      }
-      if (kGather && s > 0 && R.ovs >= 0) u = TokRaw<TokT>::load(tok_piece(R.ovb, s), ql);
-    };
-    uint32_t g = 0;
-    auto consume = [&](int it, const TileRec& R, int s, const Raw8 (&t)[kSteps], const Raw8& u) {
-      const uint32_t stage = g % kStages, par = (g / kStages) & 1;
-      wait_bar(bar(kBarAEmpty + stage), par ^ 1, p.debug, 10);
-      uint8_t* slab = smem + kOffRing + stage * kASlab;
+                for (int i = 0; i < kE; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+                for (uint32_t k = 2; k < cn; ++k) {  // third.. camera: other rigs only
+                  Raw8 qk;
+                  uint32_t tk = t[2];
 #pragma unroll
-      for (int step = 0; step < kSteps; ++step) {
-        const int r = pw * kRowsPerWarp + step * 4 + quarter;
-        float acc[8];
-        if (s == 0 || !kGather) {
-          raw8_f32_to_f8(t[step], acc);
-          store_row8<true>(slab, r, ql, acc);
-        } else {
-          TokRaw<TokT>::to_f8(t[step], acc);
-          if (R.cn[step] >= 2) {  // camera-order sum, then one divide (utils/fusion_model.py:198-201)
-            int covered = 1;
-            if (step == R.ovs) {
-              float f[8];
-              TokRaw<TokT>::to_f8(u, f);
+                  for (int j = 3; j < TDSSF_MAX_CAMS; ++j) if ((uint32_t)j == k) tk = t[j];
+                  qk.lo = ldg16(tok + (int64_t)tk * kRowBytes + c * 16);
+                  if (sizeof(TokT) == 4) {
+                    f[0] = __uint_as_float(qk.lo.x); f[1] = __uint_as_float(qk.lo.y); f[2] = __uint_as_float(qk.lo.z); f[3] = __uint_as_float(qk.lo.w);
+                  } else {
+                    TokRaw<TokT>::to_f8(qk, f);
+                  }
 #pragma unroll
-              for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
-              covered = 2;
+                  for (int i = 0; i < kE; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+                }
+#pragma unroll
+                for (int i = 0; i < kE; ++i) acc[i] = __fdiv_rn(acc[i], den);
+                uint4 o;
+                if (sizeof(TokT) == 4) {
+                  o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+                } else if (std::is_same<TokT, __half>::value) {
+                  __half2 h0 = __floats2half2_rn(acc[0], acc[1]), h1 = __floats2half2_rn(acc[2], acc[3]),
+                          h2 = __floats2half2_rn(acc[4], acc[5]), h3 = __floats2half2_rn(acc[6], acc[7]);
+                  o = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
+                                 *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
+                } else {
+                  o = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+                }
+                *reinterpret_cast<uint4*>(dst + c * 16) = o;
+              }
             }
-            if ((int)R.cn[step] > covered)  // rare: a third camera, or two two-camera rows in one quarter-warp
-              gather_rest<TokT>(slots_of(it) + (step * 4 + quarter) * 8, covered, reinterpret_cast<const TokT*>(p.tokens), p.NC, p.M,
-                                (s - 1) * kSlabK, ql, acc);
-            const float den = (float)R.cn[step];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) acc[i] = __fdiv_rn(acc[i], den);
           }
-          store_row8<TokRaw<TokT>::kSplit>(slab, r, ql, acc);
         }
-      }
-#ifndef TDSSF_EXP_NOFENCE
-      ptx::fence_proxy_async_smem();
-#endif
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(leader_full0 + 8 * stage);
-      __syncwarp();
-      ++g;
-    };
-
-    // One tile.  On entry slab 0 (point features) of tile `it` is already in flight in A; on exit slab 0 of tile
-    // it+1 is in flight in B, so the request stream never drains at a tile boundary.  The next tile's points are
-    // projected at the start of this tile and compacted near its end (one named barrier in between).
-    TileRec cur, nxt;
-    auto tile = [&](int it, Raw8 (&A)[kSteps], Raw8& uA, Raw8 (&B)[kSteps], Raw8& uB) {
-      const int64_t row0 = tile_row0(it);
-      const bool more = it + 1 < n_iters;
-#pragma unroll
-      for (int s = 0; s < kSlabs1; ++s) {
-        Raw8 (&tc)[kSteps] = (s & 1) ? B : A;   // holds slab s
-        Raw8& uc = (s & 1) ? uB : uA;
-        Raw8 (&tn)[kSteps] = (s & 1) ? A : B;   // receives slab s+1
-        Raw8& un = (s & 1) ? uA : uB;
-        { PROF_T0(t21);
-        if (s + 1 < kSlabs1) issue(row0, cur, s + 1, tn, un);
-        else if (more) issue(tile_row0(it + 1), cur, 0, tn, un);
-        PROF_ADD(p.debug, 21, t21); }
-        if (s == 0) prefetch_for_tile(it);
-        if (kGather && more && s == 0) {  // next tile's projection + compaction hide under the loads in flight
-          PROF_T0(t22);
-          fill_slots(it + 1);
-          __syncwarp();
-          compact(it + 1, nxt);
-          PROF_ADD(p.debug, 22, t22);
-        }
-        { PROF_T0(t20); consume(it, cur, s, tc, uc); PROF_ADD(p.debug, 20, t20); }
-      }
-      if (kGather && more) cur = nxt;
-    };
-
-    Raw8 ta[kSteps], tb[kSteps];
-    Raw8 ua = raw8_zero(), ub = raw8_zero();
-#pragma unroll
-    for (int step = 0; step < kSteps; ++step) { cur.base0[step] = 0; cur.cn[step] = 0; }
-    cur.ovb = 0; cur.ovs = -1;
-    nxt = cur;
-    if (n_iters > 0) {
-      if (kGather) {
-        fill_slots(0);
         __syncwarp();
-        compact(0, cur);
+        if (lane == 0) ptx::mbar_arrive_local(bar(kBarRecFull + slot));  // release: the scratch rows and s_src are visible
+        __syncwarp();
       }
-      issue(tile_row0(0), cur, 0, ta, ua);
-      PROF_T0(t24);
-      for (int it = 0; it < n_iters; it += 2) {
-        tile(it, ta, ua, tb, ub);
-        if (it + 1 < n_iters) tile(it + 1, tb, ub, ta, ua);
+    }
+  } else {
+    // =============================== producers =====================================================
+    // The instruction stream per slab is kept minimal (about 50 per thread): one source pointer per row is fetched
+    // per tile, the seven slabs are unrolled so that every load is [pointer + immediate], and the stores use
+    // precomputed 32-bit shared-memory offsets.  Three register sets: the loads of slabs s+1 and s+2 are in flight
+    // while slab s is converted (up to 96 KB per SM).
+    ptx::setmaxnreg_inc<kRegsProd>();
+    const int pw = warp - kProdWarp0;  // 0..7
+    const int quarter = lane >> 3, ql = lane & 7;
+    const uint32_t leader_full0 = ptx::mapa(bar(kBarAFull), 0);
+    const uint32_t s_src = sbase + kOffRec;
+    constexpr int kPieceBytes = kSlabK * (int)sizeof(TokT);   // 64 channels of a token row
+    constexpr bool kTok32 = sizeof(TokT) == 4 || !kGather;    // image channels arrive as fp32
+    const char* const zero_row = reinterpret_cast<const char*>(p.zeros);
+
+    // shared-memory byte offsets (from the slab start) of the thread's 8-byte (fp32 sources: two per row) or 16-byte
+    // stores, for the rows of step 0 and step 1; steps 2 and 3 are 8 rows = 1024 bytes further
+    uint32_t so_lo[2], so_hi[2], so_16[2];
+#pragma unroll
+    for (int st = 0; st < 2; ++st) {
+      const uint32_t r = (uint32_t)(pw * kRowsPerWarp + row_of(st, quarter)), sw = r & 7u;
+      const uint32_t c0 = (uint32_t)ql >> 1, hb = ((uint32_t)ql & 1u) * 8u;
+      so_lo[st] = sbase + kOffRing + r * 128u + ((c0 ^ sw) << 4) + hb;
+      so_hi[st] = sbase + kOffRing + r * 128u + (((c0 + 4u) ^ sw) << 4) + hb;
+      so_16[st] = sbase + kOffRing + r * 128u + (((uint32_t)ql ^ sw) << 4);
+    }
+
+    const char* pa[kSteps];   // image-channel source of the thread's four rows, lane offset included
+#pragma unroll
+    for (int st = 0; st < kSteps; ++st) pa[st] = zero_row;
+
+    struct Set { Raw8 a[kSteps]; };
+
+    auto issue = [&](auto S_, int it, Set& n) {
+      constexpr int S = decltype(S_)::value;
+      const int64_t row0 = tile_row0(it) + pw * kRowsPerWarp;
+      if (S == 0) {  // point features
+#pragma unroll
+        for (int st = 0; st < kSteps; ++st) {
+          const int64_t row = row0 + row_of(st, quarter);
+          const char* px = row < p.N ? reinterpret_cast<const char*>(p.x_pt) + row * (kCp * 4) + ql * 16 : zero_row;
+          n.a[st].lo = ldg16c(px);
+          n.a[st].hi = ldg16c(px + 128);
+        }
+        return;
       }
-      PROF_ADD(p.debug, 24, t24);
+      if (S == 1) {  // the tile's row sources
+        if (kGather) {
+          const int slot = it % kRecSlots;
+          wait_bar(bar(kBarRecFull + slot), (it / kRecSlots) & 1, p.debug, 12);
+#pragma unroll
+          for (int st = 0; st < kSteps; ++st)
+            pa[st] = reinterpret_cast<const char*>(ptx::lds64(s_src + (slot * kTileM + pw * kRowsPerWarp + row_of(st, quarter)) * 8)) + ql * 16;
+        } else {
+#pragma unroll
+          for (int st = 0; st < kSteps; ++st) {
+            const int64_t row = row0 + row_of(st, quarter);
+            pa[st] = row < p.N ? reinterpret_cast<const char*>(p.x_img) + row * (kCi * 4) + ql * 16 : zero_row;
+          }
+        }
+      }
+      constexpr int kOff = (S - 1) * (kTok32 ? 256 : kPieceBytes);
+#pragma unroll
+      for (int st = 0; st < kSteps; ++st) {
+        n.a[st].lo = ldg16c(pa[st] + kOff);
+        if (kTok32) n.a[st].hi = ldg16c(pa[st] + kOff + 128);
+      }
+    };
+
+    uint32_t stage = 0, phase = 0;  // A ring cursor
+    auto consume = [&](auto S_, int it, const Set& c) {
+      constexpr int S = decltype(S_)::value;
+      constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
+      wait_bar(bar(kBarAEmpty + stage), phase ^ 1, p.debug, 10);
+      const uint32_t slab_off = stage * kASlab;
+#pragma unroll
+      for (int st = 0; st < kSteps; ++st) {
+        float acc[8];
+        if (kF32) {
+          raw8_f32_to_f8(c.a[st], acc);
+          ptx::sts64(so_lo[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]));
+          ptx::sts64(so_hi[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+        } else {
+          TokRaw<TokT>::to_f8(c.a[st], acc);
+          ptx::sts128(so_16[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
+                      pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+        }
+      }
+      ptx::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        ptx::mbar_arrive_cluster(leader_full0 + 8 * stage);
+        if (kGather && S == kSlabs1 - 1) ptx::mbar_arrive_local(bar(kBarRecEmpty + it % kRecSlots));
+      }
+      __syncwarp();
+      if (++stage == kStages) { stage = 0; phase ^= 1; }
+    };
+
+    // Item stream (tile, slab) with three register sets in rotation; 7 slabs per tile, so the rotation closes after
+    // three tiles (21 items).  Item i is converted out of set i % 3 after the loads of item i+2 went into set (i+2) % 3.
+    Set R0, R1, R2;
+    auto step = [&](auto S_, int it, Set& cur, Set& nxt2) {
+      constexpr int S = decltype(S_)::value;
+      constexpr int S2 = (S + 2) % kSlabs1;
+      const int it2 = it + (S + 2 >= kSlabs1 ? 1 : 0);
+      if (it2 < n_iters) issue(std::integral_constant<int, S2>{}, it2, nxt2);
+      consume(S_, it, cur);
+    };
+    auto tile = [&](int it, Set& x, Set& y, Set& z) {  // slab 0 in x, slab 1 in y
+      step(std::integral_constant<int, 0>{}, it, x, z);
+      step(std::integral_constant<int, 1>{}, it, y, x);
+      step(std::integral_constant<int, 2>{}, it, z, y);
+      step(std::integral_constant<int, 3>{}, it, x, z);
+      step(std::integral_constant<int, 4>{}, it, y, x);
+      step(std::integral_constant<int, 5>{}, it, z, y);   // loads slab 0 of the next tile into y
+      step(std::integral_constant<int, 6>{}, it, x, z);   // loads slab 1 of the next tile into z
+    };
+    if (n_iters > 0) {
+      issue(std::integral_constant<int, 0>{}, 0, R0);
+      issue(std::integral_constant<int, 1>{}, 0, R1);
+#pragma unroll 1
+      for (int it = 0; it < n_iters; it += 3) {
+        tile(it, R0, R1, R2);
+        if (it + 1 < n_iters) tile(it + 1, R1, R2, R0);
+        if (it + 2 < n_iters) tile(it + 2, R2, R0, R1);
+      }
     }
   }
 
@@ -680,7 +684,7 @@ fused_mlp_kernel(const Params p) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::cluster_sync();
-  if (warp == 0) ptx::tmem_dealloc_2cta(tmem, 512);
+  if (warp == kMmaWarp) ptx::tmem_dealloc_2cta(tmem, 512);
 }
 
 // ---- weight packing: fp32 nn.Linear weights -> bf16 shared-memory images of both CTA ranks ------------------
@@ -737,7 +741,7 @@ static int launch(const Params& p, cudaStream_t s) {
   cfg.numAttrs = 1;
   TDSSF_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
 #ifdef TDSSF_PROFILE
-  {  // experiment builds: dump the per-role cycle counters of this launch (sums over warps) and reset them
+  {  // experiment builds: dump the barrier-wait cycle counters of this launch (sums over waiting warps) and reset them
     static int launches = 0;
     unsigned long long h[64];
     cudaStreamSynchronize(s);
@@ -745,23 +749,31 @@ static int launch(const Params& p, cudaStream_t s) {
     cudaMemset(p.debug, 0, 1024);
     if (++launches == 8) {
       const double ctas = 2.0 * clusters;
-      const char* names[64] = {};
-      names[1] = "mma wait own weights"; names[11] = "mma wait peer weights"; names[2] = "mma wait acc_free";
-      names[3] = "mma wait a_full"; names[4] = "mma wait h1_full"; names[5] = "mma wait h2_full";
-      names[7] = "epi wait acc1_full"; names[8] = "epi wait acc2_full"; names[9] = "epi wait acc3_full";
-      names[10] = "prod wait a_empty"; names[20] = "prod consume (incl. a_empty + data wait)"; names[21] = "prod issue";
-      names[22] = "prod fill_slots"; names[23] = "prod barrier+compact"; names[24] = "prod total";
-      names[25] = "mma total"; names[26] = "epi total"; names[27] = "epi1 body";
-      fprintf(stderr, "[tdssf profile] gather=%d tok_bytes=%d n_pairs=%d clusters=%d (cycles per warp, averaged)\n", (int)kGather, (int)sizeof(TokT), p.n_pairs, clusters);
-      for (int i = 0; i < 64; ++i)
-        if (names[i]) {
-          const double warps = (i >= 20 && i <= 24) || i == 10 ? 16.0 * ctas : ((i >= 7 && i <= 9) || i == 26 || i == 27 ? 4.0 * ctas : ctas / 2);
-          fprintf(stderr, "  %-44s %12.0f\n", names[i], (double)h[i] / warps);
-        }
+      struct { int code; const char* name; double warps; } rows[] = {
+          {1, "mma wait own weights", 0.5}, {11, "mma wait peer weights", 0.5}, {2, "mma wait acc_free", 0.5},
+          {3, "mma wait a_full", 0.5}, {4, "mma wait h1_full", 0.5}, {5, "mma wait h2_full", 0.5},
+          {7, "epi wait acc1_full", 4}, {8, "epi wait acc2_full", 4}, {9, "epi wait acc3_full", 4},
+          {10, "prod wait a_empty", kProducerWarps}, {12, "prod wait rec_full", kProducerWarps},
+          {13, "help wait rec_empty", kHelpWarps}};
+      fprintf(stderr, "[tdssf profile] gather=%d tok_bytes=%d n_pairs=%d clusters=%d (wait cycles per warp, averaged)\n",
+              (int)kGather, (int)sizeof(TokT), p.n_pairs, clusters);
+      for (auto& r : rows) fprintf(stderr, "  %-28s %12.0f\n", r.name, (double)h[r.code] / (r.warps * ctas));
     }
   }
 #endif
   return TDSSF_OK;
+}
+
+__device__ __align__(16) unsigned char g_zero_rows[4096];  // zero-initialised at module load, never written
+
+static const void* zero_rows() {
+  static void* z = nullptr;
+  if (!z && cudaGetSymbolAddress(&z, g_zero_rows) != cudaSuccess) z = nullptr;
+  return z;
+}
+
+static size_t scratch_bytes(int tok_dtype) {
+  return (size_t)num_sms() * kRecSlots * kTileM * kCi * (tok_dtype == TDSSF_F32 ? 4 : 2);
 }
 
 static unsigned int* debug_word() {
@@ -778,6 +790,8 @@ static unsigned int* debug_word() {
 
 extern "C" size_t tdssf_mlp_pack_bytes(void) { return tdssf::tc::kPackBytes; }
 
+extern "C" size_t tdssf_fusion_workspace_bytes(int tok_dtype) { return tdssf::tc::scratch_bytes(tok_dtype); }
+
 extern "C" int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w, void* packed, void* stream) {
   using namespace tdssf;
   TDSSF_REQUIRE(w && w->W1 && w->b1 && w->W2 && w->b2 && w->W3 && w->b3 && packed, "tdssf_mlp_pack_weights: NULL pointer");
@@ -791,7 +805,7 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
                                 const float* Rt, const float* img_hw, int B, int V, int NC, int resize_h,
                                 int resize_w, int patch, const void* tokens, int tok_dtype, int M, int Ci,
                                 const float* x_pt, const void* packed_weights, float* logits, tdssf_rec* rec_out,
-                                void* stream) {
+                                void* workspace, size_t workspace_bytes, void* stream) {
   using namespace tdssf;
   TDSSF_REQUIRE(xyz && K && Rt && img_hw && tokens && x_pt && packed_weights && logits, "tdssf_fusion_fwd: NULL pointer");
   TDSSF_REQUIRE(Ci == tc::kCi, "tdssf_fusion_fwd: built for Ci=%d token channels, got %d", tc::kCi, Ci);
@@ -800,13 +814,21 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   TDSSF_REQUIRE(patch > 0 && resize_h >= patch && resize_w >= patch, "tdssf_fusion_fwd: bad resize/patch");
   TDSSF_REQUIRE((resize_h / patch) * (resize_w / patch) == M && M <= 65536, "tdssf_fusion_fwd: M=%d does not match the patch grid", M);
   TDSSF_REQUIRE(point_stride >= 3, "tdssf_fusion_fwd: point_stride < 3");
+  if ((int64_t)B * NC * M >= (1ll << 28)) {  // token-row indices travel in 28 bits inside the kernel
+    set_error("tdssf_fusion_fwd: B*NC*M = %lld token rows exceed 2^28", (long long)B * NC * M);
+    return TDSSF_ENOSUP;
+  }
   TDSSF_REQUIRE((((uintptr_t)tokens | (uintptr_t)x_pt | (uintptr_t)logits | (uintptr_t)packed_weights) & 15) == 0 &&
                     (!rec_out || ((uintptr_t)rec_out & 15) == 0),
                 "tdssf_fusion_fwd: pointers must be 16-byte aligned");
   const int64_t N = (int64_t)B * V;
   if (N == 0) return TDSSF_OK;
   if (int rc = tdssf_check_device()) return rc;
+  TDSSF_REQUIRE(tok_dtype == TDSSF_F32 || tok_dtype == TDSSF_F16 || tok_dtype == TDSSF_BF16, "tdssf_fusion_fwd: unknown tok_dtype %d", tok_dtype);
+  TDSSF_REQUIRE(workspace && ((uintptr_t)workspace & 15) == 0 && workspace_bytes >= tc::scratch_bytes(tok_dtype),
+                "tdssf_fusion_fwd: workspace of %zu bytes needed (tdssf_fusion_workspace_bytes), got %zu", tc::scratch_bytes(tok_dtype), workspace_bytes);
   tc::Params p = {};
+  p.scratch = workspace;
   p.xyz = xyz; p.sweep_stride = sweep_stride; p.point_stride = point_stride;
   p.K = K; p.Rt = Rt; p.img_hw = img_hw;
   p.V = V; p.NC = NC; p.resize_h = resize_h; p.resize_w = resize_w; p.patch = patch; p.M = M;
@@ -814,6 +836,8 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   p.packed = (const uint8_t*)packed_weights; p.logits = logits; p.N = N;
   p.n_pairs = (int)ceil_div(N, 2 * tc::kTileM);
   p.debug = tc::debug_word();
+  p.zeros = tc::zero_rows();
+  TDSSF_REQUIRE(p.zeros != nullptr, "tdssf: could not allocate the zero row");
   cudaStream_t s = (cudaStream_t)stream;
   switch (tok_dtype) {
     case TDSSF_F32: return tc::launch<float, true>(p, s);
@@ -837,5 +861,7 @@ extern "C" int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N
   p.V = 1; p.NC = 1; p.M = 1;
   p.n_pairs = (int)ceil_div(N, 2 * tc::kTileM);
   p.debug = tc::debug_word();
+  p.zeros = tc::zero_rows();
+  TDSSF_REQUIRE(p.zeros != nullptr, "tdssf: could not allocate the zero row");
   return tc::launch<float, false>(p, (cudaStream_t)stream);
 }

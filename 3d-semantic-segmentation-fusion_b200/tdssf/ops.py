@@ -213,6 +213,18 @@ def mlp_tc(x_pt, x_img, packed) -> torch.Tensor:
     return logits.reshape(*shape, 16)
 
 
+_fusion_ws = {}  # (device index, token dtype) -> workspace tensor (scratch, reused by every call on that device)
+
+
+def _fusion_workspace(device, tok_code):
+    key = (device.index, tok_code)
+    ws = _fusion_ws.get(key)
+    if ws is None:
+        ws = torch.empty(lib.tdssf_fusion_workspace_bytes(tok_code), dtype=torch.uint8, device=device)
+        _fusion_ws[key] = ws
+    return ws
+
+
 def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None):
     """Fully fused inference: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) -> logits (B,V,16)."""
     _need_cuda(points, K, Rt, img_hw, tokens, x_pt, packed)
@@ -225,10 +237,11 @@ def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=Fa
     xp = _f32c(x_pt)
     logits = out if out is not None else torch.empty((B, V, 16), dtype=torch.float32, device=pts.device)
     rec = torch.empty((B, V, 4), dtype=torch.int32, device=pts.device) if want_rec else None
+    ws = _fusion_workspace(pts.device, _TOK_DTYPES[tokens.dtype])
     check(lib.tdssf_fusion_fwd(_ptr(pts), ss, ps, _ptr(_f32c(K)), _ptr(_f32c(Rt)), _ptr(_f32c(img_hw)), B, V, NC,
                                int(encoder.resize_height), int(encoder.resize_width), int(encoder.patch_size),
                                _ptr(tokens), _TOK_DTYPES[tokens.dtype], M, Ci, _ptr(xp), _ptr(packed), _ptr(logits),
-                               _ptr(rec), _stream(pts)), "tdssf_fusion_fwd")
+                               _ptr(rec), _ptr(ws), ws.numel(), _stream(pts)), "tdssf_fusion_fwd")
     return (logits, rec) if want_rec else logits
 
 

@@ -153,13 +153,18 @@ TDSSF_API int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w_host, void* pack
  * replaces  FeatureFusionModel.forward up to voxel_scores   utils/fusion_model.py:152-204
  * x_pt    [B*V,64] fp32 point features (PTv3 output)
  * logits  [B*V,16] fp32
- * rec_out optional [B,V] camera-assignment records (NULL to skip). */
+ * rec_out optional [B,V] camera-assignment records (NULL to skip).
+ * workspace: tdssf_fusion_workspace_bytes(tok_dtype) bytes, 16-byte aligned; holds the camera means of the points
+ *          seen by several cameras while they travel from the projecting warps to the gathering warps (contents
+ *          are scratch, nothing persists between calls). */
+TDSSF_API size_t tdssf_fusion_workspace_bytes(int tok_dtype);
 TDSSF_API int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t point_stride,
                      const float* K, const float* Rt, const float* img_hw,
                      int B, int V, int NC, int resize_h, int resize_w, int patch,
                      const void* tokens, int tok_dtype, int M, int Ci,
                      const float* x_pt, const void* packed_weights,
-                     float* logits, tdssf_rec* rec_out, void* stream);
+                     float* logits, tdssf_rec* rec_out,
+                     void* workspace, size_t workspace_bytes, void* stream);
 
 /* tensor-core MLP on pre-gathered features (used by training forward and as the unfused check).
  * x_img may be fp32 [N,384].  h1_bf16 / h2_bf16 optional saved activations. */

@@ -1,0 +1,10 @@
+#!/bin/bash
+# quick GPU iteration: tensor-core tests, experiment harness (default + profile variant)
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_tc.py -m gpu -x -q > gpurun_out/pytest_tc.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_tc.log
+tail -15 gpurun_out/pytest_tc.log
+timeout 300 python tools/exp_fused.py > gpurun_out/exp_default.json 2> gpurun_out/exp_default.err; cat gpurun_out/exp_default.json; tail -3 gpurun_out/exp_default.err
+timeout 300 python tools/exp_fused.py --tok float16 > gpurun_out/exp_f16.json 2> gpurun_out/exp_f16.err; cat gpurun_out/exp_f16.json
+timeout 300 python tools/exp_fused.py --workload config4 > gpurun_out/exp_c4.json 2> gpurun_out/exp_c4.err; cat gpurun_out/exp_c4.json
+TDSSF_LIB=$PWD/3d-semantic-segmentation-fusion_b200/build/variants/TDSSF_PROFILE/libtdssf.so timeout 300 python tools/exp_fused.py --iters 5 > gpurun_out/exp_profile.json 2> gpurun_out/exp_profile.err
+tail -30 gpurun_out/exp_profile.err
