@@ -64,7 +64,9 @@ constexpr int kOffRec = kOffBias + ((kBiasFloats * 4 + 15) & ~15);
 constexpr int kOffBar = kOffRec + kRecSlots * kTileM * 8;   // row sources: [slot][128 rows] x 8 B (a pointer)
 constexpr int kNumBars = 2 * kStages + 2 + 6 * 2 + 2 * kRecSlots;
 constexpr int kOffTmemPtr = kOffBar + kNumBars * 8;
-constexpr int kSmemBytes = kOffTmemPtr + 16;
+constexpr int kCalFloats = TDSSF_MAX_CAMS * 21 + 2;         // per helper warp: 6 x (12 extrinsic + 9 intrinsic) + (H, W)
+constexpr int kOffCal = kOffTmemPtr + 16;
+constexpr int kSmemBytes = kOffCal + kHelpWarps * kCalFloats * 4;
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget exceeded");
 static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0, "slab alignment");
 static_assert(128 * (kRegsEpi + kRegsAux) + 256 * kRegsProd <= 65536, "register budget");
@@ -204,6 +206,97 @@ __device__ __forceinline__ void store_row8(uint8_t* slab, int r, int ql, const f
 // two in the high 64 bytes, so an 8-byte-per-lane store is the minimum two wavefronts.
 __device__ __forceinline__ int row_of(int st, int q) {
   return ((q & 1) << 2) | (q >> 1) | ((st & 1) << 1) | ((st >> 1) << 3);
+}
+
+// ---- helper-warp routines -------------------------------------------------------------------------------------
+// 16 bytes of a token row as floats (4 for fp32, 8 for 16-bit) and back
+template <typename TokT> __device__ __forceinline__ void chunk_to_f(const uint4& q, float (&f)[8]) {
+  if (sizeof(TokT) == 4) {
+    f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y); f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w);
+    f[4] = f[5] = f[6] = f[7] = 0.f;
+  } else {
+    Raw8 r; r.lo = q;
+    TokRaw<TokT>::to_f8(r, f);
+  }
+}
+template <typename TokT> __device__ __forceinline__ uint4 f_to_chunk(const float (&a)[8]) {
+  if (sizeof(TokT) == 4) {
+    return make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3]));
+  } else if (std::is_same<TokT, __half>::value) {
+    __half2 h0 = __floats2half2_rn(a[0], a[1]), h1 = __floats2half2_rn(a[2], a[3]), h2 = __floats2half2_rn(a[4], a[5]),
+            h3 = __floats2half2_rn(a[6], a[7]);
+    return make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1), *reinterpret_cast<uint32_t*>(&h2),
+                      *reinterpret_cast<uint32_t*>(&h3));
+  } else {
+    return make_uint4(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]), pack_bf16(a[4], a[5]), pack_bf16(a[6], a[7]));
+  }
+}
+
+// Camera mean of two rows that are each seen by exactly two cameras (the common multi-camera case): the whole warp,
+// 16 bytes per lane and pass, every load of both rows issued before the first add.  (a + b) / 2 in fp32, rounded to the
+// token type for 16-bit tokens (utils/fusion_model.py:198-201).  second == false: only row 0 is real.
+template <typename TokT>
+__device__ __forceinline__ void mean2_rows(const char* a0, const char* b0, char* d0, const char* a1, const char* b1, char* d1,
+                                           bool second, int lane) {
+  constexpr int kChunks = kCi * (int)sizeof(TokT) / 16;  // 96 (fp32) or 48 (16-bit)
+  constexpr int kPasses = (kChunks + 31) / 32;
+  uint4 qa0[kPasses], qb0[kPasses], qa1[kPasses], qb1[kPasses];
+#pragma unroll
+  for (int i = 0; i < kPasses; ++i) {
+    const int c = i * 32 + lane;
+    if (c < kChunks) {
+      qa0[i] = ldg16(a0 + c * 16);
+      qb0[i] = ldg16(b0 + c * 16);
+      if (second) {
+        qa1[i] = ldg16(a1 + c * 16);
+        qb1[i] = ldg16(b1 + c * 16);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < kPasses; ++i) {
+    const int c = i * 32 + lane;
+    if (c < kChunks) {
+      float x[8], y[8];
+      chunk_to_f<TokT>(qa0[i], x);
+      chunk_to_f<TokT>(qb0[i], y);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);  // x/2 == x*0.5 exactly
+      *reinterpret_cast<uint4*>(d0 + c * 16) = f_to_chunk<TokT>(x);
+      if (second) {
+        chunk_to_f<TokT>(qa1[i], x);
+        chunk_to_f<TokT>(qb1[i], y);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);
+        *reinterpret_cast<uint4*>(d1 + c * 16) = f_to_chunk<TokT>(x);
+      }
+    }
+  }
+}
+
+// General case (three or more cameras; no such point exists for a ring of six cameras): camera-order sum, true divide.
+template <typename TokT>
+__device__ __noinline__ void mean_rows_general(const char* tok, uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t t4,
+                                               uint32_t t5, uint32_t cn, char* dst, int lane) {
+  const uint32_t t[TDSSF_MAX_CAMS] = {t0, t1, t2, t3, t4, t5};
+  constexpr int kRowBytes = kCi * (int)sizeof(TokT);
+  constexpr int kChunks = kRowBytes / 16;
+  const float den = (float)cn;
+  for (int c = lane; c < kChunks; c += 32) {
+    float acc[8], f[8];
+    chunk_to_f<TokT>(ldg16(tok + (int64_t)t[0] * kRowBytes + c * 16), acc);
+    for (uint32_t k = 1; k < cn && k < TDSSF_MAX_CAMS; ++k) {
+      uint32_t tk = t[1];
+#pragma unroll
+      for (int j = 2; j < TDSSF_MAX_CAMS; ++j) if ((uint32_t)j == k) tk = t[j];
+      chunk_to_f<TokT>(ldg16(tok + (int64_t)tk * kRowBytes + c * 16), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = __fadd_rn(acc[j], f[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = __fdiv_rn(acc[j], den);
+    *reinterpret_cast<uint4*>(dst + c * 16) = f_to_chunk<TokT>(acc);
+  }
 }
 
 // kGather: image channels come from the token maps through the records; else from p.x_img
@@ -404,29 +497,31 @@ fused_mlp_kernel(const Params p) {
       __syncwarp();
     } else if (kGather) {
       // =============================== helpers: projection + multi-camera rows ========================
-      // One lane per point, the cameras in sequence (calibration through the read-only L1 path: every lane of the
-      // warp reads the same 21 floats unless the tile straddles two sweeps).  The result per row is ONE source
-      // pointer for the producers: the token row of its camera, a row of zeros (no camera), or - for the ~6 % of
-      // rows seen by several cameras - a scratch row in which the warp has written the camera-order sum divided by
-      // the count (utils/fusion_model.py:195-201).  Runs up to kRecSlots tiles ahead of the producers.
+      // One lane per point, the six cameras unrolled (independent dependency chains), the sweep's calibration in a
+      // warp-private shared-memory copy.  The result per row is ONE source pointer for the producers: the token row
+      // of its camera, a row of zeros (no camera), or - for the ~6 % of rows seen by several cameras - a scratch row
+      // in which the warp has written the camera-order mean (utils/fusion_model.py:195-201).  Runs up to kRecSlots
+      // tiles ahead of the producers.
       const int hw = warp - kHelpWarp0;  // 0..2
       const char** s_src = reinterpret_cast<const char**>(smem + kOffRec);
+      float* s_cal = reinterpret_cast<float*>(smem + kOffCal) + hw * kCalFloats;  // [cam][21] + (img_h, img_w)
       constexpr int kRowBytes = kCi * (int)sizeof(TokT);
-      constexpr int kChunks = kRowBytes / 16;  // 96 (fp32) or 48 (16-bit)
       const char* const tok = reinterpret_cast<const char*>(p.tokens);
       const int64_t tok_sweep_bytes = (int64_t)p.NC * p.M * kRowBytes;
-      const int n_sweeps = (int)((p.N + p.V - 1) / p.V);
+      const uint32_t n_rows = (uint32_t)p.N, V = (uint32_t)p.V;
+      const int n_sweeps = (int)((n_rows + V - 1) / V);
       const int pf_ahead = tok_sweep_bytes <= (32 << 20) ? 2 : 1;
-      int pf_next = 0;  // first sweep whose token map has not been requested yet (lane 0 of helper 0)
+      int pf_next = 0;            // first sweep whose token map has not been requested yet (lane 0 of helper 0)
+      uint32_t b_cal = 0xffffffffu;  // sweep whose calibration is in s_cal
       for (int it = 0; it < n_iters; ++it) {
         const int slot = it % kRecSlots;
-        const int64_t row0 = tile_row0(it);
+        const uint32_t row0 = (uint32_t)tile_row0(it);
         if (it >= kRecSlots) wait_bar(bar(kBarRecEmpty + slot), ((it / kRecSlots) - 1) & 1, p.debug, 13);
         if (hw == 0 && lane == 0) {
           // L2 prefetch (TMA bulk prefetch, no registers, no completion tracking): the gather visits the token rows
           // of a sweep in random order, slab by slab; streaming the whole map of the sweeps about to be processed
           // into L2 sequentially (each CTA every gridDim-th 16 KB chunk) keeps the gather loads L2 hits.
-          const int want = min(n_sweeps, (int)(min((long long)(row0 + kTileM - 1), (long long)(p.N - 1)) / p.V) + 1 + pf_ahead);
+          const int want = min(n_sweeps, (int)(min(row0 + kTileM - 1, n_rows - 1) / V) + 1 + pf_ahead);
           for (; pf_next < want; ++pf_next) {
             const char* base = tok + (int64_t)pf_next * tok_sweep_bytes;
             for (int64_t off = (int64_t)blockIdx.x * 16384; off < tok_sweep_bytes; off += (int64_t)gridDim.x * 16384)
@@ -441,109 +536,94 @@ fused_mlp_kernel(const Params p) {
         for (int g = 0; g < kTileM / 32; ++g) {
           if ((g + it) % kHelpWarps != hw) continue;  // four 32-row groups over three warps, rotating
           const int r = g * 32 + lane;
-          const int64_t row = row0 + r;
-          uint32_t idx[TDSSF_MAX_CAMS] = {0u, 0u, 0u, 0u, 0u, 0u}, cnt = 0;  // token rows of the valid cameras, camera order
-          if (row < p.N) {
-            const uint32_t b = (uint32_t)(row / p.V);
-            const uint32_t tok_base = b * (uint32_t)(p.NC * p.M);
-            auto push = [&](uint32_t cam, uint32_t patch) {
-              const uint32_t t = tok_base + cam * (uint32_t)p.M + patch;
-#pragma unroll
-              for (int k = 0; k < TDSSF_MAX_CAMS; ++k) if ((uint32_t)k == cnt) idx[k] = t;
-              ++cnt;
-            };
-            if (p.rec_in) {
-              const uint4 rec = __ldg(reinterpret_cast<const uint4*>(p.rec_in) + row);
-              const uint32_t pk[3] = {rec.x, rec.y, rec.z};
-#pragma unroll
-              for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam)
-                if ((rec.w >> cam) & 1u) push((uint32_t)cam, (pk[cam >> 1] >> ((cam & 1) * 16)) & 0xffffu);
-            } else {
-              const int v = (int)(row - (int64_t)b * p.V);
-              const float* q = p.xyz + b * p.sweep_stride + v * p.point_stride;
-              const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-              const SweepGeom geo = make_geom(__ldg(p.img_hw + 2 * b), __ldg(p.img_hw + 2 * b + 1), p.resize_h, p.resize_w, p.patch);
-              uint32_t pk[3] = {0u, 0u, 0u}, mask = 0;
-#pragma unroll 1
-              for (int cam = 0; cam < p.NC; ++cam) {
-                CamCalib cal;
-                const float* rt = p.Rt + ((int64_t)b * p.NC + cam) * 16;
-                const float* kk = p.K + ((int64_t)b * p.NC + cam) * 9;
-#pragma unroll
-                for (int i = 0; i < 12; ++i) (&cal.r[0][0])[i] = __ldg(rt + i);
-#pragma unroll
-                for (int i = 0; i < 9; ++i) (&cal.k[0][0])[i] = __ldg(kk + i);
-                const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
-                const uint32_t f = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
-                const uint32_t sh = (uint32_t)(cam & 1) * 16u;
-                if ((cam >> 1) == 0) pk[0] |= f << sh; else if ((cam >> 1) == 1) pk[1] |= f << sh; else pk[2] |= f << sh;
-                if (pr.valid) { mask |= 1u << cam; push((uint32_t)cam, f); }
+          const uint32_t row = row0 + r;
+          const bool live = row < n_rows;
+          const uint32_t b = live ? row / V : 0xffffffffu;
+          uint32_t idx0 = 0, idx1 = 0, idxr[TDSSF_MAX_CAMS - 2] = {0u, 0u, 0u, 0u}, cnt = 0;  // token rows, camera order
+          uint32_t todo = __ballot_sync(0xffffffffu, live);
+          while (todo) {  // one pass per sweep present in the group (two only where a tile straddles sweeps)
+            const uint32_t bb = __shfl_sync(0xffffffffu, b, __ffs(todo) - 1);
+            if (bb != b_cal && !p.rec_in) {
+              __syncwarp();
+              for (int i = lane; i < p.NC * 21; i += 32) {
+                const int cam = i / 21, j = i - cam * 21;
+                s_cal[i] = j < 12 ? __ldg(p.Rt + ((int64_t)bb * p.NC + cam) * 16 + j) : __ldg(p.K + ((int64_t)bb * p.NC + cam) * 9 + (j - 12));
               }
-              if (p.rec_out) reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pk[0], pk[1], pk[2], mask | (cnt << 8));
+              if (lane < 2) s_cal[TDSSF_MAX_CAMS * 21 + lane] = __ldg(p.img_hw + 2 * bb + lane);
+              b_cal = bb;
+              __syncwarp();
             }
+            if (b == bb) {
+              const uint32_t tok_base = bb * (uint32_t)(p.NC * p.M);
+              auto push = [&](uint32_t cam, uint32_t patch) {
+                const uint32_t t = tok_base + cam * (uint32_t)p.M + patch;
+                if (cnt == 0) idx0 = t; else if (cnt == 1) idx1 = t;
+#pragma unroll
+                for (int k = 2; k < TDSSF_MAX_CAMS; ++k) if ((uint32_t)k == cnt) idxr[k - 2] = t;
+                ++cnt;
+              };
+              if (p.rec_in) {
+                const uint4 rec = __ldg(reinterpret_cast<const uint4*>(p.rec_in) + row);
+                const uint32_t pk[3] = {rec.x, rec.y, rec.z};
+#pragma unroll
+                for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam)
+                  if ((rec.w >> cam) & 1u) push((uint32_t)cam, (pk[cam >> 1] >> ((cam & 1) * 16)) & 0xffffu);
+              } else {
+                const uint32_t v = row - bb * V;
+                const float* q = p.xyz + (int64_t)bb * p.sweep_stride + (int64_t)v * p.point_stride;
+                const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+                const SweepGeom geo = make_geom(s_cal[TDSSF_MAX_CAMS * 21], s_cal[TDSSF_MAX_CAMS * 21 + 1], p.resize_h, p.resize_w, p.patch);
+                uint32_t pk[3] = {0u, 0u, 0u}, mask = 0, fl[TDSSF_MAX_CAMS];
+                bool ok[TDSSF_MAX_CAMS];
+#pragma unroll
+                for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam) {
+                  fl[cam] = 0; ok[cam] = false;
+                  if (cam < p.NC) {
+                    CamCalib cal;
+#pragma unroll
+                    for (int i = 0; i < 12; ++i) (&cal.r[0][0])[i] = s_cal[cam * 21 + i];
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) (&cal.k[0][0])[i] = s_cal[cam * 21 + 12 + i];
+                    const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
+                    fl[cam] = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
+                    ok[cam] = pr.valid;
+                  }
+                }
+#pragma unroll
+                for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam) {
+                  pk[cam >> 1] |= fl[cam] << ((cam & 1) * 16);
+                  if (ok[cam]) { mask |= 1u << cam; push((uint32_t)cam, fl[cam]); }
+                }
+                if (p.rec_out) reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pk[0], pk[1], pk[2], mask | (cnt << 8));
+              }
+            }
+            todo &= ~__ballot_sync(0xffffffffu, b == bb);
           }
           s_src[slot * kTileM + r] = cnt == 0 ? reinterpret_cast<const char*>(p.zeros)
-                                   : cnt == 1 ? tok + (int64_t)idx[0] * kRowBytes
+                                   : cnt == 1 ? tok + (int64_t)idx0 * kRowBytes
                                               : scratch + (int64_t)r * kRowBytes;
-          // rows with several cameras: the whole warp sums one row at a time, 16 bytes per lane and pass
-          uint32_t multi = __ballot_sync(0xffffffffu, cnt >= 2);
-          while (multi) {
-            const int src = __ffs(multi) - 1;
-            multi &= multi - 1;
-            const uint32_t cn = __shfl_sync(0xffffffffu, cnt, src);
-            uint32_t t[TDSSF_MAX_CAMS];
-#pragma unroll
-            for (int k = 0; k < TDSSF_MAX_CAMS; ++k) t[k] = __shfl_sync(0xffffffffu, idx[k], src);
-            char* dst = scratch + (int64_t)(g * 32 + src) * kRowBytes;
-            const float den = (float)cn;
-#pragma unroll
-            for (int c0 = 0; c0 < kChunks; c0 += 32) {
-              const int c = c0 + lane;
-              if (c < kChunks) {
-                Raw8 q0, q1;
-                q0.lo = ldg16(tok + (int64_t)t[0] * kRowBytes + c * 16);
-                q1.lo = ldg16(tok + (int64_t)t[1] * kRowBytes + c * 16);
-                float acc[8], f[8];
-                constexpr int kE = 16 / (int)sizeof(TokT);  // elements per chunk: 4 or 8
-                if (sizeof(TokT) == 4) {
-                  acc[0] = __uint_as_float(q0.lo.x); acc[1] = __uint_as_float(q0.lo.y); acc[2] = __uint_as_float(q0.lo.z); acc[3] = __uint_as_float(q0.lo.w);
-                  f[0] = __uint_as_float(q1.lo.x); f[1] = __uint_as_float(q1.lo.y); f[2] = __uint_as_float(q1.lo.z); f[3] = __uint_as_float(q1.lo.w);
-                } else {
-                  TokRaw<TokT>::to_f8(q0, acc);
-                  TokRaw<TokT>::to_f8(q1, f);
-                }
-#pragma unroll
-                for (int i = 0; i < kE; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
-                for (uint32_t k = 2; k < cn; ++k) {  // third.. camera: other rigs only
-                  Raw8 qk;
-                  uint32_t tk = t[2];
-#pragma unroll
-                  for (int j = 3; j < TDSSF_MAX_CAMS; ++j) if ((uint32_t)j == k) tk = t[j];
-                  qk.lo = ldg16(tok + (int64_t)tk * kRowBytes + c * 16);
-                  if (sizeof(TokT) == 4) {
-                    f[0] = __uint_as_float(qk.lo.x); f[1] = __uint_as_float(qk.lo.y); f[2] = __uint_as_float(qk.lo.z); f[3] = __uint_as_float(qk.lo.w);
-                  } else {
-                    TokRaw<TokT>::to_f8(qk, f);
-                  }
-#pragma unroll
-                  for (int i = 0; i < kE; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
-                }
-#pragma unroll
-                for (int i = 0; i < kE; ++i) acc[i] = __fdiv_rn(acc[i], den);
-                uint4 o;
-                if (sizeof(TokT) == 4) {
-                  o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
-                } else if (std::is_same<TokT, __half>::value) {
-                  __half2 h0 = __floats2half2_rn(acc[0], acc[1]), h1 = __floats2half2_rn(acc[2], acc[3]),
-                          h2 = __floats2half2_rn(acc[4], acc[5]), h3 = __floats2half2_rn(acc[6], acc[7]);
-                  o = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
-                                 *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
-                } else {
-                  o = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
-                }
-                *reinterpret_cast<uint4*>(dst + c * 16) = o;
-              }
-            }
+          // rows with two cameras: the whole warp averages two rows at a time
+          uint32_t two = __ballot_sync(0xffffffffu, cnt == 2);
+          while (two) {
+            const int sa = __ffs(two) - 1;
+            two &= two - 1;
+            const bool second = two != 0;
+            const int sb = second ? __ffs(two) - 1 : sa;
+            two &= two - 1;
+            const uint32_t a0 = __shfl_sync(0xffffffffu, idx0, sa), b0 = __shfl_sync(0xffffffffu, idx1, sa);
+            const uint32_t a1 = __shfl_sync(0xffffffffu, idx0, sb), b1 = __shfl_sync(0xffffffffu, idx1, sb);
+            mean2_rows<TokT>(tok + (int64_t)a0 * kRowBytes, tok + (int64_t)b0 * kRowBytes, scratch + (int64_t)(g * 32 + sa) * kRowBytes,
+                             tok + (int64_t)a1 * kRowBytes, tok + (int64_t)b1 * kRowBytes, scratch + (int64_t)(g * 32 + sb) * kRowBytes,
+                             second, lane);
+          }
+          uint32_t many = __ballot_sync(0xffffffffu, cnt > 2);
+          while (many) {
+            const int sa = __ffs(many) - 1;
+            many &= many - 1;
+            mean_rows_general<TokT>(tok, __shfl_sync(0xffffffffu, idx0, sa), __shfl_sync(0xffffffffu, idx1, sa),
+                                    __shfl_sync(0xffffffffu, idxr[0], sa), __shfl_sync(0xffffffffu, idxr[1], sa),
+                                    __shfl_sync(0xffffffffu, idxr[2], sa), __shfl_sync(0xffffffffu, idxr[3], sa),
+                                    __shfl_sync(0xffffffffu, cnt, sa), scratch + (int64_t)(g * 32 + sa) * kRowBytes, lane);
           }
         }
         __syncwarp();
@@ -814,8 +894,9 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   TDSSF_REQUIRE(patch > 0 && resize_h >= patch && resize_w >= patch, "tdssf_fusion_fwd: bad resize/patch");
   TDSSF_REQUIRE((resize_h / patch) * (resize_w / patch) == M && M <= 65536, "tdssf_fusion_fwd: M=%d does not match the patch grid", M);
   TDSSF_REQUIRE(point_stride >= 3, "tdssf_fusion_fwd: point_stride < 3");
-  if ((int64_t)B * NC * M >= (1ll << 28)) {  // token-row indices travel in 28 bits inside the kernel
-    set_error("tdssf_fusion_fwd: B*NC*M = %lld token rows exceed 2^28", (long long)B * NC * M);
+  if ((int64_t)B * NC * M >= (1ll << 32) || (int64_t)B * V >= (1ll << 31)) {  // 32-bit row arithmetic inside the kernel
+    set_error("tdssf_fusion_fwd: B*NC*M = %lld token rows / B*V = %lld points exceed the 32-bit index range",
+              (long long)B * NC * M, (long long)B * V);
     return TDSSF_ENOSUP;
   }
   TDSSF_REQUIRE((((uintptr_t)tokens | (uintptr_t)x_pt | (uintptr_t)logits | (uintptr_t)packed_weights) & 15) == 0 &&
