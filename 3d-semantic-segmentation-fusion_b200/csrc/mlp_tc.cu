@@ -39,14 +39,25 @@ constexpr int kN1 = 256, kN2 = 64, kN3 = 32 /* 16 classes padded to 32 */, kClas
 constexpr int kSlabK = 64;                           // K elements per 128-byte swizzled row
 constexpr int kSlabs1 = kK1 / kSlabK;                // 7
 constexpr int kSlabs2 = kN1 / kSlabK;                // 4
-constexpr int kStages = 5;
-constexpr int kEpiWarps = 4, kAuxWarps = 4, kProducerWarps = 8, kHelpWarps = 3;
+#ifndef TDSSF_STAGES
+#define TDSSF_STAGES 3  // A-operand ring depth; every 16 KB not taken from the unified array is L1 for the gather loads
+#endif
+constexpr int kStages = TDSSF_STAGES;
+constexpr int kEpiWarps = 8, kAuxWarps = 4, kProducerWarps = 8, kHelpWarps = 3;
 constexpr int kMmaWarp = kEpiWarps, kHelpWarp0 = kEpiWarps + 1, kProdWarp0 = kEpiWarps + kAuxWarps;
 constexpr int kThreads = 32 * (kEpiWarps + kAuxWarps + kProducerWarps);  // 512
 constexpr int kRowsPerWarp = kTileM / kProducerWarps;                    // 16
 constexpr int kSteps = kRowsPerWarp / 4;                                 // 4 rows per quarter-warp
 constexpr int kRecSlots = 3;                                             // tiles of row descriptors in flight
-constexpr int kRegsEpi = 88, kRegsAux = 128, kRegsProd = 144;            // 128*(88+128) + 256*144 = 64512
+// launch: 640 threads x 96 registers = 61440, redistributed over the roles (all of it is used)
+#ifndef TDSSF_SETS
+#define TDSSF_SETS 2  // producer register sets: slabs whose loads are in flight while one is converted, plus one
+#endif
+#if TDSSF_SETS == 3
+constexpr int kRegsEpi = 72, kRegsAux = 80, kRegsProd = 128;   // 256*72 + 128*80 + 256*128 = 61440
+#else
+constexpr int kRegsEpi = 72, kRegsAux = 128, kRegsProd = 104;  // 256*72 + 128*128 + 256*104 = 61440
+#endif
 
 // per-CTA shared-memory image (bytes)
 constexpr int kW1Slab = (kN1 / 2) * 128;   // 128 rows x 128 B = 16 KB
@@ -69,7 +80,7 @@ constexpr int kOffCal = kOffTmemPtr + 16;
 constexpr int kSmemBytes = kOffCal + kHelpWarps * kCalFloats * 4;
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget exceeded");
 static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0, "slab alignment");
-static_assert(128 * (kRegsEpi + kRegsAux) + 256 * kRegsProd <= 65536, "register budget");
+static_assert(32 * (kEpiWarps * kRegsEpi + kAuxWarps * kRegsAux + kProducerWarps * kRegsProd) <= (65536 / kThreads / 8 * 8) * kThreads, "register budget");
 
 constexpr size_t kPackBytes = 2 * (size_t)kWeightBytes + kBiasFloats * 4 + 64;
 
@@ -116,9 +127,16 @@ struct Params {
     if ((threadIdx.x & 31) == 0 && (dbg))                                                               \
       atomicAdd(reinterpret_cast<unsigned long long*>(dbg) + 2 + (code), (unsigned long long)(clock64() - var)); \
   } while (0)
+// timeline of one CTA (cluster 5, rank 0): clock64 at event `ev` of tile `it`
+#define TRACE(dbg, ev, it)                                                                                        \
+  do {                                                                                                              \
+    if ((dbg) && (threadIdx.x & 31) == 0 && ptx::cluster_id_x() == 5 && ptx::cluster_ctarank() == 0 && (it) < 32)   \
+      reinterpret_cast<unsigned long long*>(dbg)[128 + (ev) * 32 + (it)] = (unsigned long long)clock64();           \
+  } while (0)
 #else
 #define PROF_T0(var)
 #define PROF_ADD(dbg, code, var)
+#define TRACE(dbg, ev, it)
 #endif
 
 __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* debug, int code) {
@@ -147,9 +165,18 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // consumer so that the request stays in flight.
 __device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 // coherent 16-byte load: the scratch rows of multi-camera points are written by this CTA during the kernel
+#ifndef TDSSF_LDMODE
+#define TDSSF_LDMODE 0  // experiment: 0 ld.global (L1 allocate)  1 ld.global.cg (L2 only)  2 ld.global.L1::no_allocate
+#endif
 __device__ __forceinline__ uint4 ldg16c(const void* p) {
   uint4 r;
+#if TDSSF_LDMODE == 1
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+#elif TDSSF_LDMODE == 2
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+#else
   asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+#endif
   return r;
 }
 struct Raw8 { uint4 lo, hi; };
@@ -332,7 +359,7 @@ fused_mlp_kernel(const Params p) {
       ptx::mbar_init(bar(kBarAcc3Full + b), 1);
       ptx::mbar_init(bar(kBarH1Full + b), 2 * kEpiWarps);
       ptx::mbar_init(bar(kBarH2Full + b), 2 * kEpiWarps);
-      ptx::mbar_init(bar(kBarAccFree + b), 2 * kEpiWarps);
+      ptx::mbar_init(bar(kBarAccFree + b), 2 * 4);  // the four warps of column half 0
     }
     for (int s = 0; s < kRecSlots; ++s) {
       ptx::mbar_init(bar(kBarRecFull + s), kHelpWarps);
@@ -356,62 +383,82 @@ fused_mlp_kernel(const Params p) {
 
   if (warp < kEpiWarps) {
     // =============================== epilogue ======================================================
+    // Eight warps: warp w owns TMEM lanes 32*(w & 3) .. +31 (one row per thread) and column half (w >> 2) of every
+    // accumulator.  TMEM loads are software-pipelined in 16-column chunks: chunk c+1 is in flight while chunk c gets
+    // bias + ReLU + bf16 and is stored back as the A operand of the next layer.
     ptx::setmaxnreg_dec<kRegsEpi>();
-    const uint32_t lane_base = (uint32_t)warp * 32;
-    const uint32_t tlane = tmem + (lane_base << 16);
-    const int row_in_tile = (int)lane_base + lane;
+    const uint32_t q4 = (uint32_t)warp & 3u, ch = (uint32_t)warp >> 2;
+    const uint32_t tlane = tmem + ((q4 * 32u) << 16);
+    const int row_in_tile = (int)(q4 * 32u) + lane;
     const uint32_t leader_h1 = ptx::mapa(bar(kBarH1Full), 0), leader_h2 = ptx::mapa(bar(kBarH2Full), 0),
                    leader_free = ptx::mapa(bar(kBarAccFree), 0);
+    // bias + ReLU + bf16 of 16 accumulator columns
+    auto act16 = [&](const uint32_t (&v)[16], const float* bias, uint32_t (&h)[8]) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 bq = *reinterpret_cast<const float4*>(bias + 4 * j);
+        h[2 * j] = pack_bf16(fmaxf(__uint_as_float(v[4 * j]) + bq.x, 0.f), fmaxf(__uint_as_float(v[4 * j + 1]) + bq.y, 0.f));
+        h[2 * j + 1] = pack_bf16(fmaxf(__uint_as_float(v[4 * j + 2]) + bq.z, 0.f), fmaxf(__uint_as_float(v[4 * j + 3]) + bq.w, 0.f));
+      }
+    };
     for (int it = 0; it < n_iters; ++it) {
       const uint32_t buf = it & 1, par = (it >> 1) & 1;
       const int64_t row = tile_row0(it) + row_in_tile;
       const uint32_t tb = tlane + buf * 256;
-      // ---- layer 1: acc1 -> relu(+b1) -> bf16 H1, in place --------------------------------------
+      // ---- layer 1: acc1 cols [128ch, 128ch+128) -> relu(+b1) -> bf16 H1 cols [128ch, 128ch+64), in place --------
       wait_bar(bar(kBarAcc1Full + buf), par, p.debug, 7);
       ptx::tc_fence_after();
-#pragma unroll 1
-      for (int q = 0; q < kN1 / 32; ++q) {
-        uint32_t v[32], h[16];
-        ptx::tmem_ld32(tb + q * 32, v);
-        ptx::tmem_wait_ld();
+      if (warp == 0) TRACE(p.debug, 4, it);
+      {
+        uint32_t va[16], vb[16], h[8];
+        const uint32_t src = tb + ch * 128;
+        const float* bias = s_bias + ch * 128;
+        ptx::tmem_ld16(src, va);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float a = fmaxf(__uint_as_float(v[2 * j]) + s_bias[q * 32 + 2 * j], 0.f);
-          const float b = fmaxf(__uint_as_float(v[2 * j + 1]) + s_bias[q * 32 + 2 * j + 1], 0.f);
-          h[j] = pack_bf16(a, b);
+        for (int c = 0; c < 8; c += 2) {
+          ptx::tmem_wait_ld();
+          ptx::tmem_ld16(src + (c + 1) * 16, vb);
+          act16(va, bias + c * 16, h);
+          ptx::tmem_st8(src + c * 8, h);
+          ptx::tmem_wait_ld();
+          if (c + 2 < 8) ptx::tmem_ld16(src + (c + 2) * 16, va);
+          act16(vb, bias + (c + 1) * 16, h);
+          ptx::tmem_st8(src + (c + 1) * 8, h);
         }
-        ptx::tmem_st16(tb + q * 16, h);
       }
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(leader_h1 + 8 * buf);
       __syncwarp();
-      // ---- layer 2: acc2 -> relu(+b2) -> bf16 H2 --------------------------------------------------
+      if (warp == 0) TRACE(p.debug, 5, it);
+      // ---- layer 2: acc2 cols [64+32ch, +32) -> relu(+b2) -> bf16 H2 cols [192+16ch, +16) -------------------------
       wait_bar(bar(kBarAcc2Full + buf), par, p.debug, 8);
       ptx::tc_fence_after();
-#pragma unroll
-      for (int q = 0; q < kN2 / 32; ++q) {
-        uint32_t v[32], h[16];
-        ptx::tmem_ld32(tb + 128 + q * 32, v);
+      if (warp == 0) TRACE(p.debug, 6, it);
+      {
+        uint32_t va[16], vb[16], h[8];
+        const uint32_t src = tb + 64 + ch * 32, dst = tb + 192 + ch * 16;
+        const float* bias = s_bias + kN1 + ch * 32;
+        ptx::tmem_ld16(src, va);
+        ptx::tmem_ld16(src + 16, vb);
         ptx::tmem_wait_ld();
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float a = fmaxf(__uint_as_float(v[2 * j]) + s_bias[kN1 + q * 32 + 2 * j], 0.f);
-          const float b = fmaxf(__uint_as_float(v[2 * j + 1]) + s_bias[kN1 + q * 32 + 2 * j + 1], 0.f);
-          h[j] = pack_bf16(a, b);
-        }
-        ptx::tmem_st16(tb + 192 + q * 16, h);
+        act16(va, bias, h);
+        ptx::tmem_st8(dst, h);
+        act16(vb, bias + 16, h);
+        ptx::tmem_st8(dst + 8, h);
       }
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(leader_h2 + 8 * buf);
       __syncwarp();
-      // ---- layer 3: acc3 + b3 -> logits ------------------------------------------------------------
-      wait_bar(bar(kBarAcc3Full + buf), par, p.debug, 9);
-      ptx::tc_fence_after();
-      {
+      if (warp == 0) TRACE(p.debug, 7, it);
+      // ---- layer 3: acc3 + b3 -> logits (column half 0 only: 16 classes) ---------------------------------------------
+      if (ch == 0) {
+        wait_bar(bar(kBarAcc3Full + buf), par, p.debug, 9);
+        ptx::tc_fence_after();
+        if (warp == 0) TRACE(p.debug, 8, it);
         uint32_t v[16];
         ptx::tmem_ld16(tb + 224, v);
         ptx::tmem_wait_ld();
@@ -419,18 +466,20 @@ fused_mlp_kernel(const Params p) {
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_cluster(leader_free + 8 * buf);
         __syncwarp();
+        if (warp == 0) TRACE(p.debug, 9, it);
         if (row < p.N) {
           float4* dst = reinterpret_cast<float4*>(p.logits + row * kClasses);
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            dst[j] = make_float4(__uint_as_float(v[4 * j]) + s_bias[kN1 + kN2 + 4 * j],
-                                 __uint_as_float(v[4 * j + 1]) + s_bias[kN1 + kN2 + 4 * j + 1],
-                                 __uint_as_float(v[4 * j + 2]) + s_bias[kN1 + kN2 + 4 * j + 2],
-                                 __uint_as_float(v[4 * j + 3]) + s_bias[kN1 + kN2 + 4 * j + 3]);
+          for (int j = 0; j < 4; ++j) {
+            const float4 bq = *reinterpret_cast<const float4*>(s_bias + kN1 + kN2 + 4 * j);
+            dst[j] = make_float4(__uint_as_float(v[4 * j]) + bq.x, __uint_as_float(v[4 * j + 1]) + bq.y,
+                                 __uint_as_float(v[4 * j + 2]) + bq.z, __uint_as_float(v[4 * j + 3]) + bq.w);
+          }
         }
       }
     }
   } else if (warp < kProdWarp0) {
+    if (kRegsAux < 96) ptx::setmaxnreg_dec<kRegsAux>(); else ptx::setmaxnreg_inc<kRegsAux>();
     if (warp == kMmaWarp) {
       // =============================== weights + MMA issue ==========================================
       if (lane == 0) {
@@ -446,14 +495,62 @@ fused_mlp_kernel(const Params p) {
         wait_bar(bar(kBarWFull), 0, p.debug, 1);
         wait_bar(bar(kBarPeerW), 0, p.debug, 11);
         constexpr uint32_t kI1 = ptx::idesc_bf16(256, kN1), kI2 = ptx::idesc_bf16(256, kN2), kI3 = ptx::idesc_bf16(256, kN3);
+        // Event-driven issue: the layer-1 MMAs of tile t are issued slab by slab as the producers deliver them; while
+        // waiting, the thread services tile t-1, issuing its layer-2 MMAs as soon as the epilogue has written H1 and its
+        // layer-3 MMAs as soon as H2 is there, so that the small layers never wait behind a slow producer.
+        int pend = -1;          // tile whose layer 2 / layer 3 is still to be issued
+        bool need2 = false, need3 = false;
+        auto service = [&]() {
+          if (pend < 0) return;
+          const uint32_t buf = pend & 1, par = (pend >> 1) & 1, tb = tmem + buf * 256;
+          if (need2 && ptx::mbar_test_wait(bar(kBarH1Full + buf), par)) {
+            ptx::tc_fence_after();
+            TRACE(p.debug, 2, pend);
+            // layer 2: A = H1 (TMEM cols [0,64) and [128,192) of the buffer), B = W2, D = cols [64,128)
+#pragma unroll
+            for (int k = 0; k < kN1 / 16; ++k) {
+              const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
+              ptx::umma_ts_2cta(tb + 64, tb + (k < 8 ? k * 8 : 128 + (k - 8) * 8), bd, kI2, k != 0);
+            }
+            ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
+            need2 = false;
+          }
+          if (!need2 && need3 && ptx::mbar_test_wait(bar(kBarH2Full + buf), par)) {
+            ptx::tc_fence_after();
+            TRACE(p.debug, 3, pend);
+            // layer 3: A = H2 (cols [192,224)), B = W3, D = cols [224,256)
+#pragma unroll
+            for (int k = 0; k < kN2 / 16; ++k) {
+              const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
+              ptx::umma_ts_2cta(tb + 224, tb + 192 + k * 8, bd, kI3, k != 0);
+            }
+            ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
+            need3 = false;
+            pend = -1;
+          }
+        };
+        // wait on `b` while servicing the pending tile; ~2 s without progress is a protocol bug
+        auto wait_serving = [&](uint32_t b, uint32_t parity, int code) {
+          if (ptx::mbar_test_wait(b, parity)) return;
+          const long long t0 = clock64();
+          while (!ptx::mbar_test_wait(b, parity)) {
+            service();
+            if (clock64() - t0 > 4000000000LL) {
+              if (p.debug) atomicExch(p.debug, (unsigned)code | 0x80000000u);
+              __trap();
+            }
+          }
+          PROF_ADD(p.debug, code, t0);
+        };
         uint32_t stage = 0, phase = 0;  // A ring cursor
-        auto issue_l1 = [&](int it) {
+        for (int it = 0; it < n_iters; ++it) {
           const uint32_t buf = it & 1;
-          if (it >= 2) wait_bar(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, p.debug, 2);
+          if (it >= 2) wait_serving(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, 2);
           ptx::tc_fence_after();
+          TRACE(p.debug, 0, it);
 #pragma unroll 1
           for (int s = 0; s < kSlabs1; ++s) {
-            wait_bar(bar(kBarAFull + stage), phase, p.debug, 3);
+            wait_serving(bar(kBarAFull + stage), phase, 3);
             ptx::tc_fence_after();
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
@@ -463,31 +560,33 @@ fused_mlp_kernel(const Params p) {
             }
             ptx::umma_commit_2cta(bar(kBarAEmpty + stage), 3);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
+            service();
           }
           ptx::umma_commit_2cta(bar(kBarAcc1Full + buf), 3);
-        };
-        issue_l1(0);
-        for (int it = 0; it < n_iters; ++it) {
-          const uint32_t buf = it & 1, par = (it >> 1) & 1;
-          if (it + 1 < n_iters) issue_l1(it + 1);
-          // layer 2: A = H1 (TMEM cols [0,128) of the buffer), B = W2
-          wait_bar(bar(kBarH1Full + buf), par, p.debug, 4);
-          ptx::tc_fence_after();
-#pragma unroll
-          for (int k = 0; k < kN1 / 16; ++k) {
-            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
-            ptx::umma_ts_2cta(tmem + buf * 256 + 128, tmem + buf * 256 + k * 8, bd, kI2, k != 0);
+          TRACE(p.debug, 1, it);
+          // the previous tile must have its small layers issued before this one becomes the pending tile
+          if (pend >= 0) {
+            const long long t0 = clock64();
+            while (pend >= 0) {
+              service();
+              if (clock64() - t0 > 4000000000LL) {
+                if (p.debug) atomicExch(p.debug, 4u | 0x80000000u);
+                __trap();
+              }
+            }
+            PROF_ADD(p.debug, 4, t0);
           }
-          ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
-          // layer 3: A = H2 (cols [192,224)), B = W3
-          wait_bar(bar(kBarH2Full + buf), par, p.debug, 5);
-          ptx::tc_fence_after();
-#pragma unroll
-          for (int k = 0; k < kN2 / 16; ++k) {
-            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
-            ptx::umma_ts_2cta(tmem + buf * 256 + 224, tmem + buf * 256 + 192 + k * 8, bd, kI3, k != 0);
+          pend = it; need2 = true; need3 = true;
+        }
+        {
+          const long long t0 = clock64();
+          while (pend >= 0) {
+            service();
+            if (clock64() - t0 > 4000000000LL) {
+              if (p.debug) atomicExch(p.debug, 5u | 0x80000000u);
+              __trap();
+            }
           }
-          ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
         }
       }
       if (!leader && lane == 0) {
@@ -517,6 +616,7 @@ fused_mlp_kernel(const Params p) {
         const int slot = it % kRecSlots;
         const uint32_t row0 = (uint32_t)tile_row0(it);
         if (it >= kRecSlots) wait_bar(bar(kBarRecEmpty + slot), ((it / kRecSlots) - 1) & 1, p.debug, 13);
+        if (hw == 0) TRACE(p.debug, 11, it);
         if (hw == 0 && lane == 0) {
           // L2 prefetch (TMA bulk prefetch, no registers, no completion tracking): the gather visits the token rows
           // of a sweep in random order, slab by slab; streaming the whole map of the sweeps about to be processed
@@ -627,6 +727,7 @@ fused_mlp_kernel(const Params p) {
           }
         }
         __syncwarp();
+        if (hw == 0) TRACE(p.debug, 12, it);
         if (lane == 0) ptx::mbar_arrive_local(bar(kBarRecFull + slot));  // release: the scratch rows and s_src are visible
         __syncwarp();
       }
@@ -704,6 +805,7 @@ fused_mlp_kernel(const Params p) {
     auto consume = [&](auto S_, int it, const Set& c) {
       constexpr int S = decltype(S_)::value;
       constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
+      if (S == 0 && pw == 0) TRACE(p.debug, 10, it);
       wait_bar(bar(kBarAEmpty + stage), phase ^ 1, p.debug, 10);
       const uint32_t slab_off = stage * kASlab;
 #pragma unroll
@@ -729,8 +831,10 @@ fused_mlp_kernel(const Params p) {
       if (++stage == kStages) { stage = 0; phase ^= 1; }
     };
 
-    // Item stream (tile, slab) with three register sets in rotation; 7 slabs per tile, so the rotation closes after
-    // three tiles (21 items).  Item i is converted out of set i % 3 after the loads of item i+2 went into set (i+2) % 3.
+    // Item stream (tile, slab): item i is converted out of register set i % kSets after the loads of item
+    // i + kSets - 1 went into the set that item i - 1 has just left.  7 slabs per tile, so the rotation closes after
+    // kSets tiles.
+#if TDSSF_SETS == 3
     Set R0, R1, R2;
     auto step = [&](auto S_, int it, Set& cur, Set& nxt2) {
       constexpr int S = decltype(S_)::value;
@@ -758,6 +862,33 @@ fused_mlp_kernel(const Params p) {
         if (it + 2 < n_iters) tile(it + 2, R2, R0, R1);
       }
     }
+#else
+    Set R0, R1;
+    auto step = [&](auto S_, int it, Set& cur, Set& nxt) {
+      constexpr int S = decltype(S_)::value;
+      constexpr int S1 = (S + 1) % kSlabs1;
+      const int it1 = it + (S + 1 >= kSlabs1 ? 1 : 0);
+      if (it1 < n_iters) issue(std::integral_constant<int, S1>{}, it1, nxt);
+      consume(S_, it, cur);
+    };
+    auto tile = [&](int it, Set& x, Set& y) {  // slab 0 in x
+      step(std::integral_constant<int, 0>{}, it, x, y);
+      step(std::integral_constant<int, 1>{}, it, y, x);
+      step(std::integral_constant<int, 2>{}, it, x, y);
+      step(std::integral_constant<int, 3>{}, it, y, x);
+      step(std::integral_constant<int, 4>{}, it, x, y);
+      step(std::integral_constant<int, 5>{}, it, y, x);
+      step(std::integral_constant<int, 6>{}, it, x, y);   // loads slab 0 of the next tile into y
+    };
+    if (n_iters > 0) {
+      issue(std::integral_constant<int, 0>{}, 0, R0);
+#pragma unroll 1
+      for (int it = 0; it < n_iters; it += 2) {
+        tile(it, R0, R1);
+        if (it + 1 < n_iters) tile(it + 1, R1, R0);
+      }
+    }
+#endif
   }
 
   // ---- teardown ----------------------------------------------------------------------------------------
@@ -826,18 +957,31 @@ static int launch(const Params& p, cudaStream_t s) {
     unsigned long long h[64];
     cudaStreamSynchronize(s);
     cudaMemcpy(h, reinterpret_cast<unsigned long long*>(p.debug) + 2, sizeof(h), cudaMemcpyDeviceToHost);
-    cudaMemset(p.debug, 0, 1024);
+    static unsigned long long tr[13 * 32];
+    cudaMemcpy(tr, reinterpret_cast<unsigned long long*>(p.debug) + 128, sizeof(tr), cudaMemcpyDeviceToHost);
+    cudaMemset(p.debug, 0, 8192);
     if (++launches == 8) {
       const double ctas = 2.0 * clusters;
       struct { int code; const char* name; double warps; } rows[] = {
           {1, "mma wait own weights", 0.5}, {11, "mma wait peer weights", 0.5}, {2, "mma wait acc_free", 0.5},
           {3, "mma wait a_full", 0.5}, {4, "mma wait h1_full", 0.5}, {5, "mma wait h2_full", 0.5},
-          {7, "epi wait acc1_full", 4}, {8, "epi wait acc2_full", 4}, {9, "epi wait acc3_full", 4},
+          {7, "epi wait acc1_full", kEpiWarps}, {8, "epi wait acc2_full", kEpiWarps}, {9, "epi wait acc3_full", 4},
           {10, "prod wait a_empty", kProducerWarps}, {12, "prod wait rec_full", kProducerWarps},
           {13, "help wait rec_empty", kHelpWarps}};
       fprintf(stderr, "[tdssf profile] gather=%d tok_bytes=%d n_pairs=%d clusters=%d (wait cycles per warp, averaged)\n",
               (int)kGather, (int)sizeof(TokT), p.n_pairs, clusters);
       for (auto& r : rows) fprintf(stderr, "  %-28s %12.0f\n", r.name, (double)h[r.code] / (r.warps * ctas));
+      const char* ev[13] = {"mma L1 start", "mma L1 issued", "mma H1 ready", "mma H2 ready", "epi acc1 full", "epi H1 done",
+                            "epi acc2 full", "epi H2 done", "epi acc3 full", "epi acc free", "prod tile start", "help start", "help end"};
+      const unsigned long long t0 = tr[0 * 32 + 4];
+      fprintf(stderr, "  timeline of cluster 5 rank 0, cycles relative to 'mma L1 start' of tile 4\n  %-16s", "event");
+      for (int it = 4; it < 10; ++it) fprintf(stderr, " %9d", it);
+      fprintf(stderr, "\n");
+      for (int e = 0; e < 13; ++e) {
+        fprintf(stderr, "  %-16s", ev[e]);
+        for (int it = 4; it < 10; ++it) fprintf(stderr, " %9lld", (long long)(tr[e * 32 + it] - t0));
+        fprintf(stderr, "\n");
+      }
     }
   }
 #endif
@@ -859,8 +1003,8 @@ static size_t scratch_bytes(int tok_dtype) {
 static unsigned int* debug_word() {
   static unsigned int* d = nullptr;
   if (!d) {
-    if (cudaMalloc(&d, 1024) != cudaSuccess) return nullptr;
-    cudaMemset(d, 0, 1024);
+    if (cudaMalloc(&d, 8192) != cudaSuccess) return nullptr;
+    cudaMemset(d, 0, 8192);
   }
   return d;
 }
