@@ -43,20 +43,19 @@ constexpr int kSlabs2 = kN1 / kSlabK;                // 4
 #define TDSSF_STAGES 3  // A-operand ring depth; every 16 KB not taken from the unified array is L1 for the gather loads
 #endif
 constexpr int kStages = TDSSF_STAGES;
-constexpr int kEpiWarps = 8, kAuxWarps = 4, kProducerWarps = 8, kHelpWarps = 3;
-constexpr int kMmaWarp = kEpiWarps, kHelpWarp0 = kEpiWarps + 1, kProdWarp0 = kEpiWarps + kAuxWarps;
+constexpr int kEpiWarps = 8, kAuxWarps = 4, kProducerWarps = 8;
+constexpr int kMmaWarp = kEpiWarps, kProdWarp0 = kEpiWarps + kAuxWarps;
 constexpr int kThreads = 32 * (kEpiWarps + kAuxWarps + kProducerWarps);  // 512
 constexpr int kRowsPerWarp = kTileM / kProducerWarps;                    // 16
 constexpr int kSteps = kRowsPerWarp / 4;                                 // 4 rows per quarter-warp
-constexpr int kRecSlots = 3;                                             // tiles of row descriptors in flight
 // launch: 640 threads x 96 registers = 61440, redistributed over the roles (all of it is used)
 #ifndef TDSSF_SETS
-#define TDSSF_SETS 2  // producer register sets: slabs whose loads are in flight while one is converted, plus one
+#define TDSSF_SETS 3  // producer register sets: slabs whose loads are in flight while one is converted, plus one
 #endif
 #if TDSSF_SETS == 3
-constexpr int kRegsEpi = 72, kRegsAux = 80, kRegsProd = 128;   // 256*72 + 128*80 + 256*128 = 61440
+constexpr int kRegsEpi = 72, kRegsAux = 64, kRegsProd = 136;   // 256*72 + 128*64 + 256*136 = 61440
 #else
-constexpr int kRegsEpi = 72, kRegsAux = 128, kRegsProd = 104;  // 256*72 + 128*128 + 256*104 = 61440
+constexpr int kRegsEpi = 72, kRegsAux = 64, kRegsProd = 112;   // 256*72 + 128*64 + 256*112 = 55296
 #endif
 
 // per-CTA shared-memory image (bytes)
@@ -71,13 +70,10 @@ constexpr int kBiasFloats = kN1 + kN2 + kClasses;           // 336
 constexpr int kOffRing = kWeightBytes;                      // 1024-aligned
 constexpr int kASlab = kTileM * 128;                        // 16 KB
 constexpr int kOffBias = kOffRing + kStages * kASlab;       // 215040
-constexpr int kOffRec = kOffBias + ((kBiasFloats * 4 + 15) & ~15);
-constexpr int kOffBar = kOffRec + kRecSlots * kTileM * 8;   // row sources: [slot][128 rows] x 8 B (a pointer)
-constexpr int kNumBars = 2 * kStages + 2 + 6 * 2 + 2 * kRecSlots;
+constexpr int kOffBar = kOffBias + ((kBiasFloats * 4 + 15) & ~15);
+constexpr int kNumBars = 2 * kStages + 2 + 6 * 2;
 constexpr int kOffTmemPtr = kOffBar + kNumBars * 8;
-constexpr int kCalFloats = TDSSF_MAX_CAMS * 21 + 2;         // per helper warp: 6 x (12 extrinsic + 9 intrinsic) + (H, W)
-constexpr int kOffCal = kOffTmemPtr + 16;
-constexpr int kSmemBytes = kOffCal + kHelpWarps * kCalFloats * 4;
+constexpr int kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget exceeded");
 static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0, "slab alignment");
 static_assert(32 * (kEpiWarps * kRegsEpi + kAuxWarps * kRegsAux + kProducerWarps * kRegsProd) <= (65536 / kThreads / 8 * 8) * kThreads, "register budget");
@@ -96,8 +92,6 @@ enum {
   kBarH1Full = kBarAcc3Full + 2,       // [2] leader: 2*kEpiWarps arrivals
   kBarH2Full = kBarH1Full + 2,         // [2]
   kBarAccFree = kBarH2Full + 2,        // [2]
-  kBarRecFull = kBarAccFree + 2,       // [kRecSlots] kHelpWarps arrivals
-  kBarRecEmpty = kBarRecFull + kRecSlots,  // [kRecSlots] kProducerWarps arrivals
 };
 
 struct Params {
@@ -115,7 +109,9 @@ struct Params {
   int64_t N;
   int n_pairs;                 // number of 256-row tile pairs
   const void* zeros;           // >= 4 KB of zeros (source of rows without a camera / beyond N)
-  void* scratch;               // [gridDim][kRecSlots][128] token rows: means of multi-camera rows
+  const char** src_table;      // [gridDim][iters_max*128] source row of every point this CTA processes (written by its prologue)
+  void* scratch;               // [gridDim][iters_max*128] token rows: camera means of multi-camera points
+  int iters_max;               // tiles per CTA, upper bound
   unsigned int* debug;         // optional: [0] = timeout code
 };
 
@@ -260,46 +256,49 @@ template <typename TokT> __device__ __forceinline__ uint4 f_to_chunk(const float
 }
 
 // Camera mean of two rows that are each seen by exactly two cameras (the common multi-camera case): the whole warp,
-// 16 bytes per lane and pass, every load of both rows issued before the first add.  (a + b) / 2 in fp32, rounded to the
-// token type for 16-bit tokens (utils/fusion_model.py:198-201).  second == false: only row 0 is real.
-template <typename TokT>
-__device__ __forceinline__ void mean2_rows(const char* a0, const char* b0, char* d0, const char* a1, const char* b1, char* d1,
-                                           bool second, int lane) {
-  constexpr int kChunks = kCi * (int)sizeof(TokT) / 16;  // 96 (fp32) or 48 (16-bit)
-  constexpr int kPasses = (kChunks + 31) / 32;
+// 16 bytes per lane and pass.  Split in two halves so that the caller can put independent work between the loads and
+// their use.  (a + b) / 2 in fp32, rounded to the token type for 16-bit tokens (utils/fusion_model.py:198-201).
+// second == false: only row 0 is real.
+template <typename TokT> struct Mean2 {
+  static constexpr int kChunks = kCi * (int)sizeof(TokT) / 16;  // 96 (fp32) or 48 (16-bit)
+  static constexpr int kPasses = (kChunks + 31) / 32;
   uint4 qa0[kPasses], qb0[kPasses], qa1[kPasses], qb1[kPasses];
+  __device__ __forceinline__ void issue(const char* a0, const char* b0, const char* a1, const char* b1, bool second, int lane) {
 #pragma unroll
-  for (int i = 0; i < kPasses; ++i) {
-    const int c = i * 32 + lane;
-    if (c < kChunks) {
-      qa0[i] = ldg16(a0 + c * 16);
-      qb0[i] = ldg16(b0 + c * 16);
-      if (second) {
-        qa1[i] = ldg16(a1 + c * 16);
-        qb1[i] = ldg16(b1 + c * 16);
+    for (int i = 0; i < kPasses; ++i) {
+      const int c = i * 32 + lane;
+      if (c < kChunks) {
+        qa0[i] = ldg16(a0 + c * 16);
+        qb0[i] = ldg16(b0 + c * 16);
+        if (second) {
+          qa1[i] = ldg16(a1 + c * 16);
+          qb1[i] = ldg16(b1 + c * 16);
+        }
       }
     }
   }
+  __device__ __forceinline__ void finish(char* d0, char* d1, bool second, int lane) const {
 #pragma unroll
-  for (int i = 0; i < kPasses; ++i) {
-    const int c = i * 32 + lane;
-    if (c < kChunks) {
-      float x[8], y[8];
-      chunk_to_f<TokT>(qa0[i], x);
-      chunk_to_f<TokT>(qb0[i], y);
+    for (int i = 0; i < kPasses; ++i) {
+      const int c = i * 32 + lane;
+      if (c < kChunks) {
+        float x[8], y[8];
+        chunk_to_f<TokT>(qa0[i], x);
+        chunk_to_f<TokT>(qb0[i], y);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);  // x/2 == x*0.5 exactly
-      *reinterpret_cast<uint4*>(d0 + c * 16) = f_to_chunk<TokT>(x);
-      if (second) {
-        chunk_to_f<TokT>(qa1[i], x);
-        chunk_to_f<TokT>(qb1[i], y);
+        for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);  // x/2 == x*0.5 exactly
+        *reinterpret_cast<uint4*>(d0 + c * 16) = f_to_chunk<TokT>(x);
+        if (second) {
+          chunk_to_f<TokT>(qa1[i], x);
+          chunk_to_f<TokT>(qb1[i], y);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);
-        *reinterpret_cast<uint4*>(d1 + c * 16) = f_to_chunk<TokT>(x);
+          for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);
+          *reinterpret_cast<uint4*>(d1 + c * 16) = f_to_chunk<TokT>(x);
+        }
       }
     }
   }
-}
+};
 
 // General case (three or more cameras; no such point exists for a ring of six cameras): camera-order sum, true divide.
 template <typename TokT>
@@ -323,6 +322,105 @@ __device__ __noinline__ void mean_rows_general(const char* tok, uint32_t t0, uin
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = __fdiv_rn(acc[j], den);
     *reinterpret_cast<uint4*>(dst + c * 16) = f_to_chunk<TokT>(acc);
+  }
+}
+
+// projection table word of one (point, camera): 15-bit flat patch index | validity << 15
+__device__ __forceinline__ uint32_t proj_word(const CamCalib& c, float x, float y, float z, const SweepGeom& geo) {
+  const Proj pr = project_one(c, x, y, z, geo.img_h, geo.img_w);
+  return ((uint32_t)patch_index(geo, pr.u, pr.v) & 0x7fffu) | (pr.valid ? 0x8000u : 0u);
+}
+// points of a tile that belong to another sweep than the tile's first row (a tile straddling two sweeps): calibration
+// straight from global memory
+__device__ __noinline__ uint32_t proj_word_slow(const float* K, const float* Rt, const float* img_hw, int NC, uint32_t b, int cam,
+                                                float x, float y, float z, int resize_h, int resize_w, int patch) {
+  if (cam >= NC) return 0u;
+  CamCalib c;
+  const float* rt = Rt + ((int64_t)b * NC + cam) * 16;
+  const float* kk = K + ((int64_t)b * NC + cam) * 9;
+  for (int i = 0; i < 12; ++i) (&c.r[0][0])[i] = __ldg(rt + i);
+  for (int i = 0; i < 9; ++i) (&c.k[0][0])[i] = __ldg(kk + i);
+  const SweepGeom geo = make_geom(__ldg(img_hw + 2 * b), __ldg(img_hw + 2 * b + 1), resize_h, resize_w, patch);
+  return proj_word(c, x, y, z, geo);
+}
+
+// ---- prologue: projection + camera assignment of every point the CTA will process ------------------------------
+// Runs before the tile loop with all 20 warps, while the load/store unit is idle (once the producers' gather saturates
+// it, every memory instruction of another warp waits hundreds of cycles - measured: in-loop helper warps doing this work
+// halved the throughput).  One lane per point, the cameras in sequence, calibration through the read-only L1 path.
+// Result per point: ONE source pointer for the producers - the token row of its camera, a row of zeros (no camera), or,
+// for the ~6 % of points seen by several cameras, a scratch row in which the warp writes the camera-order mean
+// (utils/fusion_model.py:195-201) - and, on request, the 16-byte camera record.
+template <typename TokT, typename RowOf>
+__device__ __forceinline__ void project_rows(const Params& p, int n_iters, RowOf tile_row0, int warp, int lane) {
+  constexpr int kRowBytes = kCi * (int)sizeof(TokT);
+  const char* const tok = reinterpret_cast<const char*>(p.tokens);
+  const uint32_t n_rows = (uint32_t)p.N, V = (uint32_t)p.V;
+  const char** const table = p.src_table + (int64_t)blockIdx.x * p.iters_max * kTileM;
+  char* const scratch = reinterpret_cast<char*>(p.scratch) + (int64_t)blockIdx.x * p.iters_max * kTileM * kRowBytes;
+  const int n_groups = n_iters * (kTileM / 32);
+#pragma unroll 1
+  for (int grp = warp; grp < n_groups; grp += kThreads / 32) {
+    const int i = grp * 32 + lane;  // index of the point in the CTA's list
+    const uint32_t row = (uint32_t)tile_row0(i / kTileM) + (uint32_t)(i % kTileM);
+    uint32_t idx0 = 0, idx1 = 0, idxr[TDSSF_MAX_CAMS - 2] = {0u, 0u, 0u, 0u}, cnt = 0;
+    if (row < n_rows) {
+      const uint32_t b = row / V;
+      const float* q = p.xyz + (int64_t)b * p.sweep_stride + (int64_t)(row - b * V) * p.point_stride;
+      const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+      const SweepGeom geo = make_geom(__ldg(p.img_hw + 2 * b), __ldg(p.img_hw + 2 * b + 1), p.resize_h, p.resize_w, p.patch);
+      const uint32_t tok_base = b * (uint32_t)(p.NC * p.M);
+      uint32_t pk[3] = {0u, 0u, 0u}, mask = 0;
+#pragma unroll 2
+      for (int cam = 0; cam < p.NC; ++cam) {
+        CamCalib cal;
+        const float* rt = p.Rt + ((int64_t)b * p.NC + cam) * 16;
+        const float* kk = p.K + ((int64_t)b * p.NC + cam) * 9;
+#pragma unroll
+        for (int k = 0; k < 12; ++k) (&cal.r[0][0])[k] = __ldg(rt + k);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) (&cal.k[0][0])[k] = __ldg(kk + k);
+        const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
+        const uint32_t f = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
+        const uint32_t sh = (uint32_t)(cam & 1) * 16u;
+        if ((cam >> 1) == 0) pk[0] |= f << sh; else if ((cam >> 1) == 1) pk[1] |= f << sh; else pk[2] |= f << sh;
+        if (pr.valid) {
+          const uint32_t t = tok_base + (uint32_t)cam * (uint32_t)p.M + f;
+          if (cnt == 0) idx0 = t; else if (cnt == 1) idx1 = t;
+#pragma unroll
+          for (int k = 2; k < TDSSF_MAX_CAMS; ++k) if ((uint32_t)k == cnt) idxr[k - 2] = t;
+          mask |= 1u << cam;
+          ++cnt;
+        }
+      }
+      if (p.rec_out) reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pk[0], pk[1], pk[2], mask | (cnt << 8));
+    }
+    table[i] = cnt == 0 ? reinterpret_cast<const char*>(p.zeros)
+             : cnt == 1 ? tok + (int64_t)idx0 * kRowBytes
+                        : scratch + (int64_t)i * kRowBytes;
+    // rows with two cameras: the whole warp averages two rows at a time
+    uint32_t two = __ballot_sync(0xffffffffu, cnt == 2);
+    while (two) {
+      const int sa = __ffs(two) - 1;
+      two &= two - 1;
+      const bool second = two != 0;
+      const int sb = second ? __ffs(two) - 1 : sa;
+      two &= two - 1;
+      const uint32_t a0 = __shfl_sync(0xffffffffu, idx0, sa), b0 = __shfl_sync(0xffffffffu, idx1, sa);
+      const uint32_t a1 = __shfl_sync(0xffffffffu, idx0, sb), b1 = __shfl_sync(0xffffffffu, idx1, sb);
+      Mean2<TokT> m;
+      m.issue(tok + (int64_t)a0 * kRowBytes, tok + (int64_t)b0 * kRowBytes, tok + (int64_t)a1 * kRowBytes, tok + (int64_t)b1 * kRowBytes, second, lane);
+      m.finish(scratch + (int64_t)(grp * 32 + sa) * kRowBytes, scratch + (int64_t)(grp * 32 + sb) * kRowBytes, second, lane);
+    }
+    uint32_t many = __ballot_sync(0xffffffffu, cnt > 2);
+    while (many) {
+      const int sa = __ffs(many) - 1;
+      many &= many - 1;
+      mean_rows_general<TokT>(tok, __shfl_sync(0xffffffffu, idx0, sa), __shfl_sync(0xffffffffu, idx1, sa),
+                              __shfl_sync(0xffffffffu, idxr[0], sa), __shfl_sync(0xffffffffu, idxr[1], sa),
+                              __shfl_sync(0xffffffffu, idxr[2], sa), __shfl_sync(0xffffffffu, idxr[3], sa),
+                              __shfl_sync(0xffffffffu, cnt, sa), scratch + (int64_t)(grp * 32 + sa) * kRowBytes, lane);
+    }
   }
 }
 
@@ -361,10 +459,6 @@ fused_mlp_kernel(const Params p) {
       ptx::mbar_init(bar(kBarH2Full + b), 2 * kEpiWarps);
       ptx::mbar_init(bar(kBarAccFree + b), 2 * 4);  // the four warps of column half 0
     }
-    for (int s = 0; s < kRecSlots; ++s) {
-      ptx::mbar_init(bar(kBarRecFull + s), kHelpWarps);
-      ptx::mbar_init(bar(kBarRecEmpty + s), kProducerWarps);
-    }
     ptx::fence_mbar_init();
   }
   {  // biases (shared by both ranks) live after the two weight images
@@ -380,6 +474,19 @@ fused_mlp_kernel(const Params p) {
   ptx::cluster_sync();  // barriers initialised and TMEM allocated in both CTAs before any remote traffic
   ptx::tc_fence_after();
   const uint32_t tmem = *s_tmem;
+
+  if (warp == kMmaWarp && lane == 0) {  // the weights land while the prologue runs
+    const uint8_t* src = p.packed + (size_t)rank * kWeightBytes;
+    ptx::mbar_expect_tx(bar(kBarWFull), kWeightBytes);
+    for (int off = 0; off < kWeightBytes; off += 16384) {
+      const int n = min(16384, kWeightBytes - off);
+      ptx::bulk_g2s(sbase + kOffW1 + off, src + off, n, bar(kBarWFull));
+    }
+  }
+  if (kGather) {
+    project_rows<TokT>(p, n_iters, tile_row0, warp, lane);
+    __syncthreads();  // the CTA's source table and scratch rows are complete and visible to its producers
+  }
 
   if (warp < kEpiWarps) {
     // =============================== epilogue ======================================================
@@ -482,14 +589,6 @@ fused_mlp_kernel(const Params p) {
     if (kRegsAux < 96) ptx::setmaxnreg_dec<kRegsAux>(); else ptx::setmaxnreg_inc<kRegsAux>();
     if (warp == kMmaWarp) {
       // =============================== weights + MMA issue ==========================================
-      if (lane == 0) {
-        const uint8_t* src = p.packed + (size_t)rank * kWeightBytes;
-        ptx::mbar_expect_tx(bar(kBarWFull), kWeightBytes);
-        for (int off = 0; off < kWeightBytes; off += 16384) {
-          const int n = min(16384, kWeightBytes - off);
-          ptx::bulk_g2s(sbase + kOffW1 + off, src + off, n, bar(kBarWFull));
-        }
-      }
       if (leader && lane == 0 && n_iters > 0) {
         // B operands are read from both CTAs' shared memory: wait for our image and for the peer's
         wait_bar(bar(kBarWFull), 0, p.debug, 1);
@@ -594,143 +693,6 @@ fused_mlp_kernel(const Params p) {
         ptx::mbar_arrive_cluster(ptx::mapa(bar(kBarPeerW), 0));
       }
       __syncwarp();
-    } else if (kGather) {
-      // =============================== helpers: projection + multi-camera rows ========================
-      // One lane per point, the six cameras unrolled (independent dependency chains), the sweep's calibration in a
-      // warp-private shared-memory copy.  The result per row is ONE source pointer for the producers: the token row
-      // of its camera, a row of zeros (no camera), or - for the ~6 % of rows seen by several cameras - a scratch row
-      // in which the warp has written the camera-order mean (utils/fusion_model.py:195-201).  Runs up to kRecSlots
-      // tiles ahead of the producers.
-      const int hw = warp - kHelpWarp0;  // 0..2
-      const char** s_src = reinterpret_cast<const char**>(smem + kOffRec);
-      float* s_cal = reinterpret_cast<float*>(smem + kOffCal) + hw * kCalFloats;  // [cam][21] + (img_h, img_w)
-      constexpr int kRowBytes = kCi * (int)sizeof(TokT);
-      const char* const tok = reinterpret_cast<const char*>(p.tokens);
-      const int64_t tok_sweep_bytes = (int64_t)p.NC * p.M * kRowBytes;
-      const uint32_t n_rows = (uint32_t)p.N, V = (uint32_t)p.V;
-      const int n_sweeps = (int)((n_rows + V - 1) / V);
-      const int pf_ahead = tok_sweep_bytes <= (32 << 20) ? 2 : 1;
-      int pf_next = 0;            // first sweep whose token map has not been requested yet (lane 0 of helper 0)
-      uint32_t b_cal = 0xffffffffu;  // sweep whose calibration is in s_cal
-      for (int it = 0; it < n_iters; ++it) {
-        const int slot = it % kRecSlots;
-        const uint32_t row0 = (uint32_t)tile_row0(it);
-        if (it >= kRecSlots) wait_bar(bar(kBarRecEmpty + slot), ((it / kRecSlots) - 1) & 1, p.debug, 13);
-        if (hw == 0) TRACE(p.debug, 11, it);
-        if (hw == 0 && lane == 0) {
-          // L2 prefetch (TMA bulk prefetch, no registers, no completion tracking): the gather visits the token rows
-          // of a sweep in random order, slab by slab; streaming the whole map of the sweeps about to be processed
-          // into L2 sequentially (each CTA every gridDim-th 16 KB chunk) keeps the gather loads L2 hits.
-          const int want = min(n_sweeps, (int)(min(row0 + kTileM - 1, n_rows - 1) / V) + 1 + pf_ahead);
-          for (; pf_next < want; ++pf_next) {
-            const char* base = tok + (int64_t)pf_next * tok_sweep_bytes;
-            for (int64_t off = (int64_t)blockIdx.x * 16384; off < tok_sweep_bytes; off += (int64_t)gridDim.x * 16384)
-              ptx::prefetch_l2(base + off, (uint32_t)min((long long)16384, (long long)(tok_sweep_bytes - off)));
-          }
-          const int64_t r2 = tile_row0(it + 2);  // point features two tiles ahead: one contiguous block
-          if (it + 2 < n_iters && r2 < p.N)
-            ptx::prefetch_l2(p.x_pt + r2 * kCp, (uint32_t)(min((long long)kTileM, (long long)(p.N - r2)) * kCp * 4));
-        }
-        char* const scratch = reinterpret_cast<char*>(p.scratch) + ((int64_t)blockIdx.x * kRecSlots + slot) * kTileM * kRowBytes;
-#pragma unroll 1
-        for (int g = 0; g < kTileM / 32; ++g) {
-          if ((g + it) % kHelpWarps != hw) continue;  // four 32-row groups over three warps, rotating
-          const int r = g * 32 + lane;
-          const uint32_t row = row0 + r;
-          const bool live = row < n_rows;
-          const uint32_t b = live ? row / V : 0xffffffffu;
-          uint32_t idx0 = 0, idx1 = 0, idxr[TDSSF_MAX_CAMS - 2] = {0u, 0u, 0u, 0u}, cnt = 0;  // token rows, camera order
-          uint32_t todo = __ballot_sync(0xffffffffu, live);
-          while (todo) {  // one pass per sweep present in the group (two only where a tile straddles sweeps)
-            const uint32_t bb = __shfl_sync(0xffffffffu, b, __ffs(todo) - 1);
-            if (bb != b_cal && !p.rec_in) {
-              __syncwarp();
-              for (int i = lane; i < p.NC * 21; i += 32) {
-                const int cam = i / 21, j = i - cam * 21;
-                s_cal[i] = j < 12 ? __ldg(p.Rt + ((int64_t)bb * p.NC + cam) * 16 + j) : __ldg(p.K + ((int64_t)bb * p.NC + cam) * 9 + (j - 12));
-              }
-              if (lane < 2) s_cal[TDSSF_MAX_CAMS * 21 + lane] = __ldg(p.img_hw + 2 * bb + lane);
-              b_cal = bb;
-              __syncwarp();
-            }
-            if (b == bb) {
-              const uint32_t tok_base = bb * (uint32_t)(p.NC * p.M);
-              auto push = [&](uint32_t cam, uint32_t patch) {
-                const uint32_t t = tok_base + cam * (uint32_t)p.M + patch;
-                if (cnt == 0) idx0 = t; else if (cnt == 1) idx1 = t;
-#pragma unroll
-                for (int k = 2; k < TDSSF_MAX_CAMS; ++k) if ((uint32_t)k == cnt) idxr[k - 2] = t;
-                ++cnt;
-              };
-              if (p.rec_in) {
-                const uint4 rec = __ldg(reinterpret_cast<const uint4*>(p.rec_in) + row);
-                const uint32_t pk[3] = {rec.x, rec.y, rec.z};
-#pragma unroll
-                for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam)
-                  if ((rec.w >> cam) & 1u) push((uint32_t)cam, (pk[cam >> 1] >> ((cam & 1) * 16)) & 0xffffu);
-              } else {
-                const uint32_t v = row - bb * V;
-                const float* q = p.xyz + (int64_t)bb * p.sweep_stride + (int64_t)v * p.point_stride;
-                const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-                const SweepGeom geo = make_geom(s_cal[TDSSF_MAX_CAMS * 21], s_cal[TDSSF_MAX_CAMS * 21 + 1], p.resize_h, p.resize_w, p.patch);
-                uint32_t pk[3] = {0u, 0u, 0u}, mask = 0, fl[TDSSF_MAX_CAMS];
-                bool ok[TDSSF_MAX_CAMS];
-#pragma unroll
-                for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam) {
-                  fl[cam] = 0; ok[cam] = false;
-                  if (cam < p.NC) {
-                    CamCalib cal;
-#pragma unroll
-                    for (int i = 0; i < 12; ++i) (&cal.r[0][0])[i] = s_cal[cam * 21 + i];
-#pragma unroll
-                    for (int i = 0; i < 9; ++i) (&cal.k[0][0])[i] = s_cal[cam * 21 + 12 + i];
-                    const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
-                    fl[cam] = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
-                    ok[cam] = pr.valid;
-                  }
-                }
-#pragma unroll
-                for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam) {
-                  pk[cam >> 1] |= fl[cam] << ((cam & 1) * 16);
-                  if (ok[cam]) { mask |= 1u << cam; push((uint32_t)cam, fl[cam]); }
-                }
-                if (p.rec_out) reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pk[0], pk[1], pk[2], mask | (cnt << 8));
-              }
-            }
-            todo &= ~__ballot_sync(0xffffffffu, b == bb);
-          }
-          s_src[slot * kTileM + r] = cnt == 0 ? reinterpret_cast<const char*>(p.zeros)
-                                   : cnt == 1 ? tok + (int64_t)idx0 * kRowBytes
-                                              : scratch + (int64_t)r * kRowBytes;
-          // rows with two cameras: the whole warp averages two rows at a time
-          uint32_t two = __ballot_sync(0xffffffffu, cnt == 2);
-          while (two) {
-            const int sa = __ffs(two) - 1;
-            two &= two - 1;
-            const bool second = two != 0;
-            const int sb = second ? __ffs(two) - 1 : sa;
-            two &= two - 1;
-            const uint32_t a0 = __shfl_sync(0xffffffffu, idx0, sa), b0 = __shfl_sync(0xffffffffu, idx1, sa);
-            const uint32_t a1 = __shfl_sync(0xffffffffu, idx0, sb), b1 = __shfl_sync(0xffffffffu, idx1, sb);
-            mean2_rows<TokT>(tok + (int64_t)a0 * kRowBytes, tok + (int64_t)b0 * kRowBytes, scratch + (int64_t)(g * 32 + sa) * kRowBytes,
-                             tok + (int64_t)a1 * kRowBytes, tok + (int64_t)b1 * kRowBytes, scratch + (int64_t)(g * 32 + sb) * kRowBytes,
-                             second, lane);
-          }
-          uint32_t many = __ballot_sync(0xffffffffu, cnt > 2);
-          while (many) {
-            const int sa = __ffs(many) - 1;
-            many &= many - 1;
-            mean_rows_general<TokT>(tok, __shfl_sync(0xffffffffu, idx0, sa), __shfl_sync(0xffffffffu, idx1, sa),
-                                    __shfl_sync(0xffffffffu, idxr[0], sa), __shfl_sync(0xffffffffu, idxr[1], sa),
-                                    __shfl_sync(0xffffffffu, idxr[2], sa), __shfl_sync(0xffffffffu, idxr[3], sa),
-                                    __shfl_sync(0xffffffffu, cnt, sa), scratch + (int64_t)(g * 32 + sa) * kRowBytes, lane);
-          }
-        }
-        __syncwarp();
-        if (hw == 0) TRACE(p.debug, 12, it);
-        if (lane == 0) ptx::mbar_arrive_local(bar(kBarRecFull + slot));  // release: the scratch rows and s_src are visible
-        __syncwarp();
-      }
     }
   } else {
     // =============================== producers =====================================================
@@ -742,7 +704,7 @@ fused_mlp_kernel(const Params p) {
     const int pw = warp - kProdWarp0;  // 0..7
     const int quarter = lane >> 3, ql = lane & 7;
     const uint32_t leader_full0 = ptx::mapa(bar(kBarAFull), 0);
-    const uint32_t s_src = sbase + kOffRec;
+    const char* const* const table = p.src_table + (int64_t)blockIdx.x * p.iters_max * kTileM + pw * kRowsPerWarp;
     constexpr int kPieceBytes = kSlabK * (int)sizeof(TokT);   // 64 channels of a token row
     constexpr bool kTok32 = sizeof(TokT) == 4 || !kGather;    // image channels arrive as fp32
     const char* const zero_row = reinterpret_cast<const char*>(p.zeros);
@@ -760,8 +722,19 @@ fused_mlp_kernel(const Params p) {
     }
 
     const char* pa[kSteps];   // image-channel source of the thread's four rows, lane offset included
+    const char* pn[kSteps];   // the same for the next tile (read from the CTA's source table one tile ahead)
 #pragma unroll
-    for (int st = 0; st < kSteps; ++st) pa[st] = zero_row;
+    for (int st = 0; st < kSteps; ++st) { pa[st] = zero_row; pn[st] = zero_row; }
+    auto load_sources = [&](int it) {
+      if (!kGather || it >= n_iters) return;
+#pragma unroll
+      for (int st = 0; st < kSteps; ++st) {
+        uint64_t v;
+        asm volatile("ld.global.b64 %0, [%1];" : "=l"(v) : "l"(table + it * kTileM + row_of(st, quarter)));
+        pn[st] = reinterpret_cast<const char*>(v);
+      }
+    };
+    load_sources(0);
 
     struct Set { Raw8 a[kSteps]; };
 
@@ -780,11 +753,9 @@ fused_mlp_kernel(const Params p) {
       }
       if (S == 1) {  // the tile's row sources
         if (kGather) {
-          const int slot = it % kRecSlots;
-          wait_bar(bar(kBarRecFull + slot), (it / kRecSlots) & 1, p.debug, 12);
 #pragma unroll
-          for (int st = 0; st < kSteps; ++st)
-            pa[st] = reinterpret_cast<const char*>(ptx::lds64(s_src + (slot * kTileM + pw * kRowsPerWarp + row_of(st, quarter)) * 8)) + ql * 16;
+          for (int st = 0; st < kSteps; ++st) pa[st] = pn[st] + ql * 16;
+          load_sources(it + 1);
         } else {
 #pragma unroll
           for (int st = 0; st < kSteps; ++st) {
@@ -825,7 +796,6 @@ fused_mlp_kernel(const Params p) {
       __syncwarp();
       if (lane == 0) {
         ptx::mbar_arrive_cluster(leader_full0 + 8 * stage);
-        if (kGather && S == kSlabs1 - 1) ptx::mbar_arrive_local(bar(kBarRecEmpty + it % kRecSlots));
       }
       __syncwarp();
       if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -957,7 +927,7 @@ static int launch(const Params& p, cudaStream_t s) {
     unsigned long long h[64];
     cudaStreamSynchronize(s);
     cudaMemcpy(h, reinterpret_cast<unsigned long long*>(p.debug) + 2, sizeof(h), cudaMemcpyDeviceToHost);
-    static unsigned long long tr[13 * 32];
+    static unsigned long long tr[16 * 32];
     cudaMemcpy(tr, reinterpret_cast<unsigned long long*>(p.debug) + 128, sizeof(tr), cudaMemcpyDeviceToHost);
     cudaMemset(p.debug, 0, 8192);
     if (++launches == 8) {
@@ -966,18 +936,18 @@ static int launch(const Params& p, cudaStream_t s) {
           {1, "mma wait own weights", 0.5}, {11, "mma wait peer weights", 0.5}, {2, "mma wait acc_free", 0.5},
           {3, "mma wait a_full", 0.5}, {4, "mma wait h1_full", 0.5}, {5, "mma wait h2_full", 0.5},
           {7, "epi wait acc1_full", kEpiWarps}, {8, "epi wait acc2_full", kEpiWarps}, {9, "epi wait acc3_full", 4},
-          {10, "prod wait a_empty", kProducerWarps}, {12, "prod wait rec_full", kProducerWarps},
-          {13, "help wait rec_empty", kHelpWarps}};
+          {10, "prod wait a_empty", kProducerWarps}};
       fprintf(stderr, "[tdssf profile] gather=%d tok_bytes=%d n_pairs=%d clusters=%d (wait cycles per warp, averaged)\n",
               (int)kGather, (int)sizeof(TokT), p.n_pairs, clusters);
       for (auto& r : rows) fprintf(stderr, "  %-28s %12.0f\n", r.name, (double)h[r.code] / (r.warps * ctas));
-      const char* ev[13] = {"mma L1 start", "mma L1 issued", "mma H1 ready", "mma H2 ready", "epi acc1 full", "epi H1 done",
-                            "epi acc2 full", "epi H2 done", "epi acc3 full", "epi acc free", "prod tile start", "help start", "help end"};
+      const char* ev[16] = {"mma L1 start", "mma L1 issued", "mma H1 ready", "mma H2 ready", "epi acc1 full", "epi H1 done",
+                            "epi acc2 full", "epi H2 done", "epi acc3 full", "epi acc free", "prod tile start", "help start", "help end",
+                            "help pair issued", "help projected", "help pts loaded"};
       const unsigned long long t0 = tr[0 * 32 + 4];
       fprintf(stderr, "  timeline of cluster 5 rank 0, cycles relative to 'mma L1 start' of tile 4\n  %-16s", "event");
       for (int it = 4; it < 10; ++it) fprintf(stderr, " %9d", it);
       fprintf(stderr, "\n");
-      for (int e = 0; e < 13; ++e) {
+      for (int e = 0; e < 16; ++e) {
         fprintf(stderr, "  %-16s", ev[e]);
         for (int it = 4; it < 10; ++it) fprintf(stderr, " %9lld", (long long)(tr[e * 32 + it] - t0));
         fprintf(stderr, "\n");
@@ -996,8 +966,16 @@ static const void* zero_rows() {
   return z;
 }
 
-static size_t scratch_bytes(int tok_dtype) {
-  return (size_t)num_sms() * kRecSlots * kTileM * kCi * (tok_dtype == TDSSF_F32 ? 4 : 2);
+// tiles per CTA (upper bound) for N points on this device
+static int iters_max_for(int64_t N) {
+  const int n_pairs = (int)ceil_div(N, 2 * kTileM);
+  const int clusters = std::max(1, std::min(num_sms() / 2, n_pairs));
+  return (int)ceil_div(n_pairs, clusters);
+}
+// workspace = source table [ctas][iters_max*128] x 8 B, then scratch rows [ctas][iters_max*128] x one token row
+static size_t table_bytes(int64_t N) { return ((size_t)num_sms() * iters_max_for(N) * kTileM * 8 + 255) & ~(size_t)255; }
+static size_t scratch_bytes(int64_t N, int tok_dtype) {
+  return table_bytes(N) + (size_t)num_sms() * iters_max_for(N) * kTileM * kCi * (tok_dtype == TDSSF_F32 ? 4 : 2);
 }
 
 static unsigned int* debug_word() {
@@ -1014,7 +992,9 @@ static unsigned int* debug_word() {
 
 extern "C" size_t tdssf_mlp_pack_bytes(void) { return tdssf::tc::kPackBytes; }
 
-extern "C" size_t tdssf_fusion_workspace_bytes(int tok_dtype) { return tdssf::tc::scratch_bytes(tok_dtype); }
+extern "C" size_t tdssf_fusion_workspace_bytes(int B, int V, int tok_dtype) {
+  return tdssf::tc::scratch_bytes((int64_t)std::max(B, 0) * std::max(V, 0), tok_dtype);
+}
 
 extern "C" int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w, void* packed, void* stream) {
   using namespace tdssf;
@@ -1036,7 +1016,7 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   TDSSF_REQUIRE(NC >= 1 && NC <= TDSSF_MAX_CAMS, "tdssf_fusion_fwd: NC=%d not in 1..%d", NC, TDSSF_MAX_CAMS);
   TDSSF_REQUIRE(B >= 0 && V >= 0 && B < 65536, "tdssf_fusion_fwd: bad B/V");
   TDSSF_REQUIRE(patch > 0 && resize_h >= patch && resize_w >= patch, "tdssf_fusion_fwd: bad resize/patch");
-  TDSSF_REQUIRE((resize_h / patch) * (resize_w / patch) == M && M <= 65536, "tdssf_fusion_fwd: M=%d does not match the patch grid", M);
+  TDSSF_REQUIRE((resize_h / patch) * (resize_w / patch) == M && M <= 32768, "tdssf_fusion_fwd: M=%d does not match the patch grid (or exceeds 32768)", M);
   TDSSF_REQUIRE(point_stride >= 3, "tdssf_fusion_fwd: point_stride < 3");
   if ((int64_t)B * NC * M >= (1ll << 32) || (int64_t)B * V >= (1ll << 31)) {  // 32-bit row arithmetic inside the kernel
     set_error("tdssf_fusion_fwd: B*NC*M = %lld token rows / B*V = %lld points exceed the 32-bit index range",
@@ -1050,10 +1030,13 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   if (N == 0) return TDSSF_OK;
   if (int rc = tdssf_check_device()) return rc;
   TDSSF_REQUIRE(tok_dtype == TDSSF_F32 || tok_dtype == TDSSF_F16 || tok_dtype == TDSSF_BF16, "tdssf_fusion_fwd: unknown tok_dtype %d", tok_dtype);
-  TDSSF_REQUIRE(workspace && ((uintptr_t)workspace & 15) == 0 && workspace_bytes >= tc::scratch_bytes(tok_dtype),
-                "tdssf_fusion_fwd: workspace of %zu bytes needed (tdssf_fusion_workspace_bytes), got %zu", tc::scratch_bytes(tok_dtype), workspace_bytes);
+  TDSSF_REQUIRE(workspace && ((uintptr_t)workspace & 255) == 0 && workspace_bytes >= tc::scratch_bytes(N, tok_dtype),
+                "tdssf_fusion_fwd: 256-byte aligned workspace of %zu bytes needed (tdssf_fusion_workspace_bytes), got %zu",
+                tc::scratch_bytes(N, tok_dtype), workspace_bytes);
   tc::Params p = {};
-  p.scratch = workspace;
+  p.src_table = reinterpret_cast<const char**>(workspace);
+  p.scratch = reinterpret_cast<char*>(workspace) + tc::table_bytes(N);
+  p.iters_max = tc::iters_max_for(N);
   p.xyz = xyz; p.sweep_stride = sweep_stride; p.point_stride = point_stride;
   p.K = K; p.Rt = Rt; p.img_hw = img_hw;
   p.V = V; p.NC = NC; p.resize_h = resize_h; p.resize_w = resize_w; p.patch = patch; p.M = M;

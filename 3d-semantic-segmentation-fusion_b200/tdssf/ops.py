@@ -213,15 +213,15 @@ def mlp_tc(x_pt, x_img, packed) -> torch.Tensor:
     return logits.reshape(*shape, 16)
 
 
-_fusion_ws = {}  # (device index, token dtype) -> workspace tensor (scratch, reused by every call on that device)
+_fusion_ws = {}  # device index -> workspace tensor (scratch; grown on demand, reused by every call on that device)
 
 
-def _fusion_workspace(device, tok_code):
-    key = (device.index, tok_code)
-    ws = _fusion_ws.get(key)
-    if ws is None:
-        ws = torch.empty(lib.tdssf_fusion_workspace_bytes(tok_code), dtype=torch.uint8, device=device)
-        _fusion_ws[key] = ws
+def _fusion_workspace(device, B, V, tok_code):
+    need = lib.tdssf_fusion_workspace_bytes(B, V, tok_code)
+    ws = _fusion_ws.get(device.index)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, dtype=torch.uint8, device=device)
+        _fusion_ws[device.index] = ws
     return ws
 
 
@@ -237,7 +237,7 @@ def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=Fa
     xp = _f32c(x_pt)
     logits = out if out is not None else torch.empty((B, V, 16), dtype=torch.float32, device=pts.device)
     rec = torch.empty((B, V, 4), dtype=torch.int32, device=pts.device) if want_rec else None
-    ws = _fusion_workspace(pts.device, _TOK_DTYPES[tokens.dtype])
+    ws = _fusion_workspace(pts.device, B, V, _TOK_DTYPES[tokens.dtype])
     check(lib.tdssf_fusion_fwd(_ptr(pts), ss, ps, _ptr(_f32c(K)), _ptr(_f32c(Rt)), _ptr(_f32c(img_hw)), B, V, NC,
                                int(encoder.resize_height), int(encoder.resize_width), int(encoder.patch_size),
                                _ptr(tokens), _TOK_DTYPES[tokens.dtype], M, Ci, _ptr(xp), _ptr(packed), _ptr(logits),

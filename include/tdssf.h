@@ -154,10 +154,11 @@ TDSSF_API int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w_host, void* pack
  * x_pt    [B*V,64] fp32 point features (PTv3 output)
  * logits  [B*V,16] fp32
  * rec_out optional [B,V] camera-assignment records (NULL to skip).
- * workspace: tdssf_fusion_workspace_bytes(tok_dtype) bytes, 16-byte aligned; holds the camera means of the points
- *          seen by several cameras while they travel from the projecting warps to the gathering warps (contents
- *          are scratch, nothing persists between calls). */
-TDSSF_API size_t tdssf_fusion_workspace_bytes(int tok_dtype);
+ * workspace: tdssf_fusion_workspace_bytes(B, V, tok_dtype) bytes, 256-byte aligned.  Holds, per point, the address of
+ *          the token row the gather will read, and for the points seen by several cameras their camera mean (worst case
+ *          one token row per point; only the rows of such points are ever touched).  Scratch: nothing persists between
+ *          calls, and the same workspace may serve any call with B*V not larger than it was sized for. */
+TDSSF_API size_t tdssf_fusion_workspace_bytes(int B, int V, int tok_dtype);
 TDSSF_API int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t point_stride,
                      const float* K, const float* Rt, const float* img_hw,
                      int B, int V, int NC, int resize_h, int resize_w, int patch,
