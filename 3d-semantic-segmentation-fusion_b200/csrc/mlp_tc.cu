@@ -6,25 +6,25 @@
 // shares every B operand: W1 (256x448 bf16 = 224 KB) does not fit one SM's shared memory, split in two
 // N-halves of 112 KB it stays resident for the whole kernel, and so do W2 and W3.
 //
-// 16 warps in four warpgroups, register budgets rebalanced with setmaxnreg (launch: 128 per thread):
-//   warps 0-3    epilogue (88 regs): TMEM -> registers -> bias/ReLU -> bf16 -> TMEM (A operand of the next layer);
-//                last layer -> logits to HBM
-//   warp  4      TMEM allocation, weight load (cp.async.bulk), MMA issue (leader CTA only)          (64 regs)
-//   warps 5-6    projectors: lidar->camera->pixel->patch for the tile's points, up to kRecSlots tiles ahead of the
-//                producers; 16-byte camera records go to a shared-memory ring (and to rec_out).  Lane 0 of warp 5
-//                also streams the token maps of the sweeps about to be gathered into L2 (cp.async.bulk.prefetch).
-//   warp  7      idle (keeps the warpgroups aligned)
-//   warps 8-15   producers (176 regs): per 64-channel K slab, gather + camera mean from the L2-resident token maps
-//                (or dense loads), fp32 -> bf16, written in the 128B-swizzled K-major layout the UMMA descriptor
-//                expects.  A thread owns a quarter of four rows; the loads of slab s+1 (first and second camera of
-//                every row, 2 x 64 registers) are in flight while slab s is converted.
+// Per CTA (20 warps, five warpgroups; register budgets rebalanced with setmaxnreg, launch: 96 per thread):
+//   prologue     all warps: projection lidar->camera->pixel->patch of every point the CTA will process, one source
+//                pointer per point into the workspace (token row / zero row / scratch row holding the camera mean of
+//                a multi-camera point), camera records to rec_out.  Done up front because once the gather saturates
+//                the load/store unit every memory instruction of another warp queues for hundreds of cycles.
+//   warps 0-7    epilogue (72 regs): TMEM -> registers -> bias/ReLU -> bf16 -> TMEM (A operand of the next layer), in
+//                16-column chunks with the next TMEM load in flight; last layer -> logits to HBM
+//   warp  8      TMEM allocation, weight load (cp.async.bulk), event-driven MMA issue (leader CTA only)   (64 regs)
+//   warps 9-11   idle after the prologue (keep the warpgroups aligned)
+//   warps 12-19  producers (136 regs): per 64-channel K slab, gather of the rows' sources (L2/HBM) with
+//                [pointer + immediate] loads, fp32 -> bf16, written in the 128B-swizzled K-major layout the UMMA
+//                descriptor expects.  A thread owns a quarter of four rows; three register sets: the loads of slabs
+//                s+1 and s+2 are in flight while slab s is converted.
 //
-// TMEM (512 columns) holds two 256-column tile buffers; inside a buffer the layer-1 accumulator is
-// overwritten in place by its own bf16 activation (H1), and the layer-2/3 accumulators and H2 reuse
-// columns of it that have already been consumed:
-//   [0,256) acc1   ->   [0,128) H1 | [128,192) acc2 | [192,224) H2 | [224,256) acc3
-// MMA issue order  L1(t+1), L2(t), L3(t)  overlaps the layer-1 epilogue of tile t with the layer-1
-// MMAs of tile t+1.
+// TMEM (512 columns) holds two 256-column tile buffers; inside a buffer the layer-1 accumulator is overwritten in
+// place by its own bf16 activation (H1), and the layer-2/3 accumulators and H2 reuse columns already consumed:
+//   [0,256) acc1   ->   [0,64) H1 lo | [64,128) acc2 | [128,192) H1 hi | [192,224) H2 | [224,256) acc3
+// The MMA thread issues layer 1 of tile t+1 slab by slab as the producers deliver, and services tile t (layer 2 when
+// H1 is written, layer 3 when H2 is written) in between, so the small layers never wait behind a slow producer.
 #include <algorithm>
 #include <type_traits>
 #include "project.cuh"
@@ -484,8 +484,10 @@ fused_mlp_kernel(const Params p) {
     }
   }
   if (kGather) {
+    if (warp == 0) TRACE(p.debug, 11, 0);
     project_rows<TokT>(p, n_iters, tile_row0, warp, lane);
-    __syncthreads();  // the CTA's source table and scratch rows are complete and visible to its producers
+    __syncthreads();
+    if (warp == 0) TRACE(p.debug, 12, 0);  // the CTA's source table and scratch rows are complete and visible to its producers
   }
 
   if (warp < kEpiWarps) {
@@ -943,6 +945,9 @@ static int launch(const Params& p, cudaStream_t s) {
       const char* ev[16] = {"mma L1 start", "mma L1 issued", "mma H1 ready", "mma H2 ready", "epi acc1 full", "epi H1 done",
                             "epi acc2 full", "epi H2 done", "epi acc3 full", "epi acc free", "prod tile start", "help start", "help end",
                             "help pair issued", "help projected", "help pts loaded"};
+      fprintf(stderr, "  prologue %lld cycles; first L1 start %lld, last acc free %lld cycles after the prologue start (%d tiles)\n",
+              (long long)(tr[12 * 32] - tr[11 * 32]), (long long)(tr[0] - tr[11 * 32]),
+              (long long)(tr[9 * 32 + (p.n_pairs / clusters) - 1] - tr[11 * 32]), p.n_pairs / clusters);
       const unsigned long long t0 = tr[0 * 32 + 4];
       fprintf(stderr, "  timeline of cluster 5 rank 0, cycles relative to 'mma L1 start' of tile 4\n  %-16s", "event");
       for (int it = 4; it < 10; ++it) fprintf(stderr, " %9d", it);
