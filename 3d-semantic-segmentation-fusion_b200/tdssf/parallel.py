@@ -1,0 +1,103 @@
+"""Sweep-sharded data parallelism for the fusion path: one process per GPU, no collective on the data path.
+
+The reference is single-process (`main_train.py`, `utils/train.py:30-75`, `utils/test.py:60-95`); every row of the hot
+path is independent per sweep, so N GPUs each take their own sweeps of the DataLoader batch.  Only two quantities ever
+cross ranks, both outside the kernels and both tiny:
+
+    * the int64 confusion matrix of the evaluation loop (utils/evaluation.py:35-42, summed over batches at
+      utils/test.py:82-87) — SUM, exact in integers;
+    * the fusion-MLP gradients of one training step (132 k fp32 parameters, mlp.{0,2,4}) — averaged, in ONE flat
+      bucket (0.5 MB: launch-latency bound on NVSwitch, so one collective, not six).
+
+`torch.distributed` is the plumbing (NCCL on the GPUs, gloo in the CPU tests); nothing here touches the kernels.
+"""
+from __future__ import annotations
+
+from typing import Iterable, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def world():
+    """(rank, world_size) of the default group; (0, 1) when torch.distributed is not initialised."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_bounds(n_items: int, rank: int, world_size: int) -> tuple[int, int]:
+    """Contiguous [lo, hi) slice of `n_items` sweeps owned by `rank`: sizes differ by at most one, earlier ranks take
+    the larger shares, every sweep is owned exactly once."""
+    if world_size < 1 or not 0 <= rank < world_size:
+        raise ValueError(f"bad rank/world_size {rank}/{world_size}")
+    if n_items < 0:
+        raise ValueError("n_items must be >= 0")
+    base, extra = divmod(n_items, world_size)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_sweeps(batch: Sequence, rank: int | None = None, world_size: int | None = None):
+    """This rank's sweeps of a batch.  Tensors are sliced along dim 0 (views, no copy); lists/tuples (the reference's
+    per-sweep calibration lists, utils/dataset.py collate) are sliced as lists."""
+    r, w = world()
+    rank = r if rank is None else rank
+    world_size = w if world_size is None else world_size
+    lo, hi = shard_bounds(len(batch), rank, world_size)
+    return batch[lo:hi]
+
+
+def allreduce_confusion(cm: torch.Tensor) -> torch.Tensor:
+    """In-place SUM of the int64 (C,C) confusion matrix over ranks (exact); returns `cm`."""
+    if cm.dtype != torch.int64:
+        raise TypeError("confusion matrix must be int64")
+    if world()[1] > 1:
+        dist.all_reduce(cm, op=dist.ReduceOp.SUM)
+    return cm
+
+
+def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
+    """Average the gradients of `params` over ranks through one flat fp32 bucket; parameters without a gradient on
+    this rank contribute zeros (a rank whose sweeps had no valid labels).  Returns the bucket's element count."""
+    params = [p for p in params if p.requires_grad]
+    if not params:
+        return 0
+    _, w = world()
+    dev = params[0].device
+    flat = torch.zeros(sum(p.numel() for p in params), dtype=torch.float32, device=dev)
+    off = 0
+    for p in params:
+        if p.grad is not None:
+            flat[off:off + p.numel()].copy_(p.grad.reshape(-1))
+        off += p.numel()
+    if w > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        flat.div_(w)
+    off = 0
+    for p in params:
+        g = flat[off:off + p.numel()].view_as(p)
+        if p.grad is None:
+            p.grad = g.clone()
+        else:
+            p.grad.copy_(g)
+        off += p.numel()
+    return flat.numel()
+
+
+def max_over_ranks(value: float, device=None) -> float:
+    """MAX of a per-rank scalar (device times in bench.py)."""
+    if world()[1] == 1:
+        return float(value)
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value: float, device=None) -> float:
+    """SUM of a per-rank scalar (loss / correct / point counters of the evaluation loop, utils/test.py:75-81)."""
+    if world()[1] == 1:
+        return float(value)
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
