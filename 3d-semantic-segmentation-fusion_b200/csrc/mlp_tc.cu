@@ -73,7 +73,10 @@ constexpr int kOffBias = kOffRing + kStages * kASlab;       // 215040
 constexpr int kOffBar = kOffBias + ((kBiasFloats * 4 + 15) & ~15);
 constexpr int kNumBars = 2 * kStages + 2 + 6 * 2;
 constexpr int kOffTmemPtr = kOffBar + kNumBars * 8;
+constexpr int kOffGroupCtr = kOffTmemPtr + 8;              // prologue: next unclaimed group of 32 points
 constexpr int kSmemBytes = kOffTmemPtr + 16;
+constexpr int kCalFloats = 24;                              // per camera: rows 0..2 of lidar->camera, K, 3 floats of padding
+constexpr int kCalStageFloats = kStages * kASlab / 4;       // the idle A ring holds the calibration during the prologue
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget exceeded");
 static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0, "slab alignment");
 static_assert(32 * (kEpiWarps * kRegsEpi + kAuxWarps * kRegsAux + kProducerWarps * kRegsProd) <= (65536 / kThreads / 8 * 8) * kThreads, "register budget");
@@ -98,9 +101,8 @@ struct Params {
   // source of the 384 image channels: gather (tokens + projection or records) or a dense matrix
   const float* xyz; int64_t sweep_stride, point_stride;
   const float* K; const float* Rt; const float* img_hw;
-  int V, NC, resize_h, resize_w, patch, M;
+  int B, V, NC, resize_h, resize_w, patch, M;
   const void* tokens;
-  const tdssf_rec* rec_in;     // optional precomputed records (skips the projection)
   tdssf_rec* rec_out;          // optional
   const float* x_img;          // dense mode
   const float* x_pt;           // [N,64]
@@ -325,102 +327,198 @@ __device__ __noinline__ void mean_rows_general(const char* tok, uint32_t t0, uin
   }
 }
 
-// projection table word of one (point, camera): 15-bit flat patch index | validity << 15
-__device__ __forceinline__ uint32_t proj_word(const CamCalib& c, float x, float y, float z, const SweepGeom& geo) {
-  const Proj pr = project_one(c, x, y, z, geo.img_h, geo.img_w);
-  return ((uint32_t)patch_index(geo, pr.u, pr.v) & 0x7fffu) | (pr.valid ? 0x8000u : 0u);
-}
-// points of a tile that belong to another sweep than the tile's first row (a tile straddling two sweeps): calibration
-// straight from global memory
-__device__ __noinline__ uint32_t proj_word_slow(const float* K, const float* Rt, const float* img_hw, int NC, uint32_t b, int cam,
-                                                float x, float y, float z, int resize_h, int resize_w, int patch) {
-  if (cam >= NC) return 0u;
-  CamCalib c;
-  const float* rt = Rt + ((int64_t)b * NC + cam) * 16;
-  const float* kk = K + ((int64_t)b * NC + cam) * 9;
-  for (int i = 0; i < 12; ++i) (&c.r[0][0])[i] = __ldg(rt + i);
-  for (int i = 0; i < 9; ++i) (&c.k[0][0])[i] = __ldg(kk + i);
-  const SweepGeom geo = make_geom(__ldg(img_hw + 2 * b), __ldg(img_hw + 2 * b + 1), resize_h, resize_w, patch);
-  return proj_word(c, x, y, z, geo);
+// Camera assignment of one point: token rows of the cameras that see it (camera order), their number, and the fields of
+// the 16-byte camera record.
+struct PointCams {
+  uint32_t idx0, idx1, idx2, idx3, idx4, idx5, cnt, mask, pk0, pk1, pk2;
+};
+
+// All cameras of one point through the exact path.  Only used for a warp in which some point passes the division-free
+// filter for more than two cameras (impossible for a ring of six cameras; kept for arbitrary calibrations).
+__device__ __noinline__ PointCams project_point_all(const float* K, const float* Rt, int NC, int M, uint32_t b, float x, float y,
+                                                    float z, SweepGeom geo) {
+  PointCams r = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  const uint32_t tok_base = b * (uint32_t)(NC * M);
+  for (int cam = 0; cam < NC; ++cam) {
+    CamCalib cal;
+    const float* rt = Rt + ((int64_t)b * NC + cam) * 16;
+    const float* kk = K + ((int64_t)b * NC + cam) * 9;
+    for (int k = 0; k < 12; ++k) (&cal.r[0][0])[k] = __ldg(rt + k);
+    for (int k = 0; k < 9; ++k) (&cal.k[0][0])[k] = __ldg(kk + k);
+    const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
+    const uint32_t f = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
+    const uint32_t w = f << ((uint32_t)(cam & 1) * 16u);
+    if ((cam >> 1) == 0) r.pk0 |= w; else if ((cam >> 1) == 1) r.pk1 |= w; else r.pk2 |= w;
+    if (pr.valid) {
+      const uint32_t t = tok_base + (uint32_t)cam * (uint32_t)M + f;
+      switch (r.cnt) {
+        case 0: r.idx0 = t; break;
+        case 1: r.idx1 = t; break;
+        case 2: r.idx2 = t; break;
+        case 3: r.idx3 = t; break;
+        case 4: r.idx4 = t; break;
+        default: r.idx5 = t; break;
+      }
+      r.mask |= 1u << cam;
+      ++r.cnt;
+    }
+  }
+  return r;
 }
 
 // ---- prologue: projection + camera assignment of every point the CTA will process ------------------------------
 // Runs before the tile loop with all 20 warps, while the load/store unit is idle (once the producers' gather saturates
 // it, every memory instruction of another warp waits hundreds of cycles - measured: in-loop helper warps doing this work
-// halved the throughput).  One lane per point, the cameras in sequence, calibration through the read-only L1 path.
+// halved the throughput).  One lane per point.  Pass 1 takes every camera up to the homogeneous image coordinates
+// (27 flops) and applies a division-free, conservative visibility filter; the (at most two) cameras a point passes for
+// are kept in registers and only those go through pass 2: the IEEE divisions, the exact validity test and the patch
+// index.  Bit-identical to running the exact path on all cameras, at about a third of the instructions.
 // Result per point: ONE source pointer for the producers - the token row of its camera, a row of zeros (no camera), or,
 // for the ~6 % of points seen by several cameras, a scratch row in which the warp writes the camera-order mean
 // (utils/fusion_model.py:195-201) - and, on request, the 16-byte camera record.
 template <typename TokT, typename RowOf>
-__device__ __forceinline__ void project_rows(const Params& p, int n_iters, RowOf tile_row0, int warp, int lane) {
+__device__ __forceinline__ void project_rows(const Params& p, uint32_t cal_addr, uint32_t ctr_addr, int n_iters, RowOf tile_row0,
+                                             int lane) {
   constexpr int kRowBytes = kCi * (int)sizeof(TokT);
+  constexpr uint32_t kFull = 0xffffffffu;
   const char* const tok = reinterpret_cast<const char*>(p.tokens);
   const uint32_t n_rows = (uint32_t)p.N, V = (uint32_t)p.V;
   const char** const table = p.src_table + (int64_t)blockIdx.x * p.iters_max * kTileM;
   char* const scratch = reinterpret_cast<char*>(p.scratch) + (int64_t)blockIdx.x * p.iters_max * kTileM * kRowBytes;
   const int n_groups = n_iters * (kTileM / 32);
+  const bool want_rec = p.rec_out != nullptr;
+  SweepGeom geo = make_geom(1.f, 1.f, p.resize_h, p.resize_w, p.patch);  // grid fields are per launch; sizes per sweep
+  const uint32_t f_inv = (uint32_t)patch_index(geo, -1.f, -1.f) & 0xffffu;  // patch of a camera that does not see the point
+  // groups of 32 points are claimed dynamically (the camera means make their cost uneven); the next group's point is
+  // loaded while the current one is processed
+  auto claim = [&]() {
+    int g = 0;
+    if (lane == 0) g = (int)ptx::atom_add_shared(ctr_addr, 1u);
+    return __shfl_sync(kFull, g, 0);
+  };
+  struct Pt { uint32_t row, b; float x, y, z; };
+  auto fetch = [&](int g) {
+    Pt t = {0xffffffffu, 0u, 0.f, 0.f, 0.f};
+    if (g < n_groups) {
+      const int i = g * 32 + lane;
+      t.row = (uint32_t)tile_row0(i / kTileM) + (uint32_t)(i % kTileM);
+      if (t.row < n_rows) {
+        t.b = t.row / V;
+        const float* q = p.xyz + (int64_t)t.b * p.sweep_stride + (int64_t)(t.row - t.b * V) * p.point_stride;
+        t.x = __ldg(q), t.y = __ldg(q + 1), t.z = __ldg(q + 2);
+      }
+    }
+    return t;
+  };
+  int grp = claim();
+  Pt nxt = fetch(grp);
 #pragma unroll 1
-  for (int grp = warp; grp < n_groups; grp += kThreads / 32) {
+  while (grp < n_groups) {
     const int i = grp * 32 + lane;  // index of the point in the CTA's list
-    const uint32_t row = (uint32_t)tile_row0(i / kTileM) + (uint32_t)(i % kTileM);
-    uint32_t idx0 = 0, idx1 = 0, idxr[TDSSF_MAX_CAMS - 2] = {0u, 0u, 0u, 0u}, cnt = 0;
+    const Pt cur = nxt;
+    const int grp_next = claim();
+    nxt = fetch(grp_next);
+    const uint32_t row = cur.row, b = cur.b;
+    const float x = cur.x, y = cur.y, z = cur.z;
+    PointCams pc = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    uint32_t nc = 0, ca = 0, cb = 0;
+    Homog ha = {0.f, 0.f, 0.f, 1.f}, hb = ha;
+    PROF_T0(t_p1);
     if (row < n_rows) {
-      const uint32_t b = row / V;
-      const float* q = p.xyz + (int64_t)b * p.sweep_stride + (int64_t)(row - b * V) * p.point_stride;
-      const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-      const SweepGeom geo = make_geom(__ldg(p.img_hw + 2 * b), __ldg(p.img_hw + 2 * b + 1), p.resize_h, p.resize_w, p.patch);
-      const uint32_t tok_base = b * (uint32_t)(p.NC * p.M);
-      uint32_t pk[3] = {0u, 0u, 0u}, mask = 0;
-#pragma unroll 2
-      for (int cam = 0; cam < p.NC; ++cam) {
-        CamCalib cal;
-        const float* rt = p.Rt + ((int64_t)b * p.NC + cam) * 16;
-        const float* kk = p.K + ((int64_t)b * p.NC + cam) * 9;
+      const float2 hw = ptx::lds64_ro(cal_addr + (uint32_t)(p.B * p.NC) * (kCalFloats * 4u) + b * 8u);
+      geo.img_h = hw.x;
+      geo.img_w = hw.y;
+      // ---- pass 1: all cameras, no division; calibration from the staged copy, six 16-byte loads per camera ----
+      const uint32_t cal_b = cal_addr + b * (uint32_t)p.NC * (kCalFloats * 4u);
 #pragma unroll
-        for (int k = 0; k < 12; ++k) (&cal.r[0][0])[k] = __ldg(rt + k);
-#pragma unroll
-        for (int k = 0; k < 9; ++k) (&cal.k[0][0])[k] = __ldg(kk + k);
-        const Proj pr = project_one(cal, x, y, z, geo.img_h, geo.img_w);
-        const uint32_t f = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
-        const uint32_t sh = (uint32_t)(cam & 1) * 16u;
-        if ((cam >> 1) == 0) pk[0] |= f << sh; else if ((cam >> 1) == 1) pk[1] |= f << sh; else pk[2] |= f << sh;
-        if (pr.valid) {
-          const uint32_t t = tok_base + (uint32_t)cam * (uint32_t)p.M + f;
-          if (cnt == 0) idx0 = t; else if (cnt == 1) idx1 = t;
-#pragma unroll
-          for (int k = 2; k < TDSSF_MAX_CAMS; ++k) if ((uint32_t)k == cnt) idxr[k - 2] = t;
-          mask |= 1u << cam;
-          ++cnt;
+      for (int cam = 0; cam < TDSSF_MAX_CAMS; ++cam) {
+        if (cam < p.NC) {
+          const uint32_t a = cal_b + (uint32_t)cam * (kCalFloats * 4u);
+          const float4 r0 = ptx::lds128_ro(a), r1 = ptx::lds128_ro(a + 16), r2 = ptx::lds128_ro(a + 32);
+          const float4 k0 = ptx::lds128_ro(a + 48), k1 = ptx::lds128_ro(a + 64), k2 = ptx::lds128_ro(a + 80);
+          const CamCalib cal = {{{r0.x, r0.y, r0.z, r0.w}, {r1.x, r1.y, r1.z, r1.w}, {r2.x, r2.y, r2.z, r2.w}},
+                                {{k0.x, k0.y, k0.z}, {k0.w, k1.x, k1.y}, {k1.z, k1.w, k2.x}}};
+          const Homog h = project_homog(cal, x, y, z);
+          if (maybe_visible(h, geo.img_h, geo.img_w)) {
+            if (nc == 0) { ha = h; ca = cam; } else if (nc == 1) { hb = h; cb = cam; }
+            ++nc;
+          }
         }
       }
-      if (p.rec_out) reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pk[0], pk[1], pk[2], mask | (cnt << 8));
     }
+    const bool overflow = __any_sync(kFull, nc > 2);
+    PROF_ADD(p.debug, 20, t_p1);
+    PROF_T0(t_p2);
+    if (overflow) {
+      if (row < n_rows) {
+        geo.scale_h = __fdiv_rn((float)p.resize_h, fmaxf(geo.img_h, 1e-6f));
+        geo.scale_w = __fdiv_rn((float)p.resize_w, fmaxf(geo.img_w, 1e-6f));
+        pc = project_point_all(p.K, p.Rt, p.NC, p.M, b, x, y, z, geo);
+      }
+    } else {
+      // ---- pass 2: the candidates, exact ----
+      if (nc) {
+        geo.scale_h = __fdiv_rn((float)p.resize_h, fmaxf(geo.img_h, 1e-6f));  // utils/fusion_model.py:117-121
+        geo.scale_w = __fdiv_rn((float)p.resize_w, fmaxf(geo.img_w, 1e-6f));
+      }
+      const uint32_t tok_base = b * (uint32_t)(p.NC * p.M);
+      pc.pk0 = pc.pk1 = pc.pk2 = f_inv | (f_inv << 16);
+#pragma unroll 1
+      for (uint32_t s = 0; s < 2; ++s) {
+        if (!__any_sync(kFull, nc > s)) break;
+        if (nc > s) {
+          const Proj pr = project_finish(ha, geo.img_h, geo.img_w);
+          const uint32_t f = (uint32_t)patch_index(geo, pr.u, pr.v) & 0xffffu;
+          if (want_rec) {
+            const uint32_t sh = (ca & 1u) * 16u, keep = ~(0xffffu << sh), w = f << sh;
+            if ((ca >> 1) == 0) pc.pk0 = (pc.pk0 & keep) | w;
+            else if ((ca >> 1) == 1) pc.pk1 = (pc.pk1 & keep) | w;
+            else pc.pk2 = (pc.pk2 & keep) | w;
+          }
+          if (pr.valid) {
+            const uint32_t t = tok_base + ca * (uint32_t)p.M + f;
+            if (pc.cnt == 0) pc.idx0 = t; else pc.idx1 = t;
+            pc.mask |= 1u << ca;
+            ++pc.cnt;
+          }
+        }
+        ha = hb;
+        ca = cb;
+      }
+    }
+    if (want_rec && row < n_rows)
+      reinterpret_cast<uint4*>(p.rec_out)[row] = make_uint4(pc.pk0, pc.pk1, pc.pk2, pc.mask | (pc.cnt << 8));
+    const uint32_t cnt = pc.cnt;
+    PROF_ADD(p.debug, 21, t_p2);
+    PROF_T0(t_mean);
     table[i] = cnt == 0 ? reinterpret_cast<const char*>(p.zeros)
-             : cnt == 1 ? tok + (int64_t)idx0 * kRowBytes
+             : cnt == 1 ? tok + (int64_t)pc.idx0 * kRowBytes
                         : scratch + (int64_t)i * kRowBytes;
     // rows with two cameras: the whole warp averages two rows at a time
-    uint32_t two = __ballot_sync(0xffffffffu, cnt == 2);
+    uint32_t two = __ballot_sync(kFull, cnt == 2);
     while (two) {
       const int sa = __ffs(two) - 1;
       two &= two - 1;
       const bool second = two != 0;
       const int sb = second ? __ffs(two) - 1 : sa;
       two &= two - 1;
-      const uint32_t a0 = __shfl_sync(0xffffffffu, idx0, sa), b0 = __shfl_sync(0xffffffffu, idx1, sa);
-      const uint32_t a1 = __shfl_sync(0xffffffffu, idx0, sb), b1 = __shfl_sync(0xffffffffu, idx1, sb);
+      const uint32_t a0 = __shfl_sync(kFull, pc.idx0, sa), b0 = __shfl_sync(kFull, pc.idx1, sa);
+      const uint32_t a1 = __shfl_sync(kFull, pc.idx0, sb), b1 = __shfl_sync(kFull, pc.idx1, sb);
       Mean2<TokT> m;
       m.issue(tok + (int64_t)a0 * kRowBytes, tok + (int64_t)b0 * kRowBytes, tok + (int64_t)a1 * kRowBytes, tok + (int64_t)b1 * kRowBytes, second, lane);
       m.finish(scratch + (int64_t)(grp * 32 + sa) * kRowBytes, scratch + (int64_t)(grp * 32 + sb) * kRowBytes, second, lane);
     }
-    uint32_t many = __ballot_sync(0xffffffffu, cnt > 2);
+    uint32_t many = __ballot_sync(kFull, cnt > 2);
     while (many) {
       const int sa = __ffs(many) - 1;
       many &= many - 1;
-      mean_rows_general<TokT>(tok, __shfl_sync(0xffffffffu, idx0, sa), __shfl_sync(0xffffffffu, idx1, sa),
-                              __shfl_sync(0xffffffffu, idxr[0], sa), __shfl_sync(0xffffffffu, idxr[1], sa),
-                              __shfl_sync(0xffffffffu, idxr[2], sa), __shfl_sync(0xffffffffu, idxr[3], sa),
-                              __shfl_sync(0xffffffffu, cnt, sa), scratch + (int64_t)(grp * 32 + sa) * kRowBytes, lane);
+      mean_rows_general<TokT>(tok, __shfl_sync(kFull, pc.idx0, sa), __shfl_sync(kFull, pc.idx1, sa),
+                              __shfl_sync(kFull, pc.idx2, sa), __shfl_sync(kFull, pc.idx3, sa),
+                              __shfl_sync(kFull, pc.idx4, sa), __shfl_sync(kFull, pc.idx5, sa),
+                              __shfl_sync(kFull, cnt, sa), scratch + (int64_t)(grp * 32 + sa) * kRowBytes, lane);
     }
+    PROF_ADD(p.debug, 22, t_mean);
+    grp = grp_next;
   }
 }
 
@@ -461,6 +559,16 @@ fused_mlp_kernel(const Params p) {
     }
     ptx::fence_mbar_init();
   }
+  if (kGather) {  // calibration of every camera of the launch into the A ring, which is idle until the tile loop starts
+    const int n_cams = p.B * p.NC;  // host: n_cams * kCalFloats + 2 * B <= kCalStageFloats
+    float* s_cal = reinterpret_cast<float*>(smem + kOffRing);
+    for (int i = threadIdx.x; i < n_cams * kCalFloats; i += kThreads) {
+      const int cam = i / kCalFloats, j = i - cam * kCalFloats;
+      s_cal[i] = j < 12 ? __ldg(p.Rt + (int64_t)cam * 16 + j) : j < 21 ? __ldg(p.K + (int64_t)cam * 9 + (j - 12)) : 0.f;
+    }
+    for (int i = threadIdx.x; i < 2 * p.B; i += kThreads) s_cal[n_cams * kCalFloats + i] = __ldg(p.img_hw + i);
+    if (threadIdx.x == 0) *reinterpret_cast<volatile uint32_t*>(smem + kOffGroupCtr) = 0u;
+  }
   {  // biases (shared by both ranks) live after the two weight images
     const float* gb = reinterpret_cast<const float*>(p.packed + 2 * (size_t)kWeightBytes);
     for (int i = threadIdx.x; i < kBiasFloats; i += kThreads) s_bias[i] = __ldg(gb + i);
@@ -485,8 +593,10 @@ fused_mlp_kernel(const Params p) {
   }
   if (kGather) {
     if (warp == 0) TRACE(p.debug, 11, 0);
-    project_rows<TokT>(p, n_iters, tile_row0, warp, lane);
+    project_rows<TokT>(p, sbase + kOffRing, sbase + kOffGroupCtr, n_iters, tile_row0, lane);
+    PROF_T0(t_sync);
     __syncthreads();
+    PROF_ADD(p.debug, 23, t_sync);
     if (warp == 0) TRACE(p.debug, 12, 0);  // the CTA's source table and scratch rows are complete and visible to its producers
   }
 
@@ -938,10 +1048,12 @@ static int launch(const Params& p, cudaStream_t s) {
           {1, "mma wait own weights", 0.5}, {11, "mma wait peer weights", 0.5}, {2, "mma wait acc_free", 0.5},
           {3, "mma wait a_full", 0.5}, {4, "mma wait h1_full", 0.5}, {5, "mma wait h2_full", 0.5},
           {7, "epi wait acc1_full", kEpiWarps}, {8, "epi wait acc2_full", kEpiWarps}, {9, "epi wait acc3_full", 4},
-          {10, "prod wait a_empty", kProducerWarps}};
+          {10, "prod wait a_empty", kProducerWarps}, {20, "prologue pass 1 (sum of groups)", kThreads / 32},
+          {21, "prologue pass 2", kThreads / 32}, {22, "prologue camera means", kThreads / 32},
+          {23, "prologue wait for slowest warp", kThreads / 32}};
       fprintf(stderr, "[tdssf profile] gather=%d tok_bytes=%d n_pairs=%d clusters=%d (wait cycles per warp, averaged)\n",
               (int)kGather, (int)sizeof(TokT), p.n_pairs, clusters);
-      for (auto& r : rows) fprintf(stderr, "  %-28s %12.0f\n", r.name, (double)h[r.code] / (r.warps * ctas));
+      for (auto& r : rows) fprintf(stderr, "  %-34s %12.0f\n", r.name, (double)h[r.code] / (r.warps * ctas));
       const char* ev[16] = {"mma L1 start", "mma L1 issued", "mma H1 ready", "mma H2 ready", "epi acc1 full", "epi H1 done",
                             "epi acc2 full", "epi H2 done", "epi acc3 full", "epi acc free", "prod tile start", "help start", "help end",
                             "help pair issued", "help projected", "help pts loaded"};
@@ -1038,26 +1150,38 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   TDSSF_REQUIRE(workspace && ((uintptr_t)workspace & 255) == 0 && workspace_bytes >= tc::scratch_bytes(N, tok_dtype),
                 "tdssf_fusion_fwd: 256-byte aligned workspace of %zu bytes needed (tdssf_fusion_workspace_bytes), got %zu",
                 tc::scratch_bytes(N, tok_dtype), workspace_bytes);
-  tc::Params p = {};
-  p.src_table = reinterpret_cast<const char**>(workspace);
-  p.scratch = reinterpret_cast<char*>(workspace) + tc::table_bytes(N);
-  p.iters_max = tc::iters_max_for(N);
-  p.xyz = xyz; p.sweep_stride = sweep_stride; p.point_stride = point_stride;
-  p.K = K; p.Rt = Rt; p.img_hw = img_hw;
-  p.V = V; p.NC = NC; p.resize_h = resize_h; p.resize_w = resize_w; p.patch = patch; p.M = M;
-  p.tokens = tokens; p.rec_in = nullptr; p.rec_out = rec_out; p.x_img = nullptr; p.x_pt = x_pt;
-  p.packed = (const uint8_t*)packed_weights; p.logits = logits; p.N = N;
-  p.n_pairs = (int)ceil_div(N, 2 * tc::kTileM);
-  p.debug = tc::debug_word();
-  p.zeros = tc::zero_rows();
-  TDSSF_REQUIRE(p.zeros != nullptr, "tdssf: could not allocate the zero row");
+  const void* zeros = tc::zero_rows();
+  TDSSF_REQUIRE(zeros != nullptr, "tdssf: could not allocate the zero row");
   cudaStream_t s = (cudaStream_t)stream;
-  switch (tok_dtype) {
-    case TDSSF_F32: return tc::launch<float, true>(p, s);
-    case TDSSF_F16: return tc::launch<__half, true>(p, s);
-    case TDSSF_BF16: return tc::launch<__nv_bfloat16, true>(p, s);
-    default: set_error("tdssf_fusion_fwd: unknown tok_dtype %d", tok_dtype); return TDSSF_EINVAL;
+  // The kernel stages the calibration of all its sweeps in shared memory: at most `b_max` sweeps per launch (84 for six
+  // cameras), more are processed in consecutive launches that reuse the workspace.
+  const int b_max = std::max(1, tc::kCalStageFloats / (NC * tc::kCalFloats + 2));
+  const size_t tok_row = (size_t)tc::kCi * (tok_dtype == TDSSF_F32 ? 4 : 2);
+  for (int b0 = 0; b0 < B; b0 += b_max) {
+    const int Bc = std::min(b_max, B - b0);
+    const int64_t Nc = (int64_t)Bc * V, row0 = (int64_t)b0 * V;
+    tc::Params p = {};
+    p.src_table = reinterpret_cast<const char**>(workspace);
+    p.scratch = reinterpret_cast<char*>(workspace) + tc::table_bytes(Nc);
+    p.iters_max = tc::iters_max_for(Nc);
+    p.xyz = xyz + (int64_t)b0 * sweep_stride; p.sweep_stride = sweep_stride; p.point_stride = point_stride;
+    p.K = K + (int64_t)b0 * NC * 9; p.Rt = Rt + (int64_t)b0 * NC * 16; p.img_hw = img_hw + 2 * (int64_t)b0;
+    p.B = Bc; p.V = V; p.NC = NC; p.resize_h = resize_h; p.resize_w = resize_w; p.patch = patch; p.M = M;
+    p.tokens = reinterpret_cast<const char*>(tokens) + (size_t)b0 * NC * M * tok_row;
+    p.rec_out = rec_out ? rec_out + row0 : nullptr; p.x_img = nullptr; p.x_pt = x_pt + row0 * tc::kCp;
+    p.packed = (const uint8_t*)packed_weights; p.logits = logits + row0 * tc::kClasses; p.N = Nc;
+    p.n_pairs = (int)ceil_div(Nc, 2 * tc::kTileM);
+    p.debug = tc::debug_word();
+    p.zeros = zeros;
+    int rc;
+    switch (tok_dtype) {
+      case TDSSF_F32: rc = tc::launch<float, true>(p, s); break;
+      case TDSSF_F16: rc = tc::launch<__half, true>(p, s); break;
+      default: rc = tc::launch<__nv_bfloat16, true>(p, s); break;
+    }
+    if (rc != TDSSF_OK) return rc;
   }
+  return TDSSF_OK;
 }
 
 extern "C" int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N, const void* packed_weights,
@@ -1071,7 +1195,7 @@ extern "C" int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N
   if (int rc = tdssf_check_device()) return rc;
   tc::Params p = {};
   p.x_img = x_img; p.x_pt = x_pt; p.packed = (const uint8_t*)packed_weights; p.logits = logits; p.N = N;
-  p.V = 1; p.NC = 1; p.M = 1;
+  p.B = 1; p.V = 1; p.NC = 1; p.M = 1;
   p.n_pairs = (int)ceil_div(N, 2 * tc::kTileM);
   p.debug = tc::debug_word();
   p.zeros = tc::zero_rows();

@@ -42,8 +42,14 @@ struct Proj {
   bool valid;
 };
 
-__device__ __forceinline__ Proj project_one(const CamCalib& c, float x, float y, float z,
-                                            float img_h, float img_w) {
+// Homogeneous image coordinates of one (point, camera): everything of the projector before the perspective divide.
+struct Homog {
+  float cam_z;       // depth in the camera frame
+  float p0, p1;      // K rows 0,1 applied to the camera-frame point
+  float den;         // clamp(K row 2 applied, min=1e-12), NaN kept like torch does
+};
+
+__device__ __forceinline__ Homog project_homog(const CamCalib& c, float x, float y, float z) {
   float cam[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -58,16 +64,41 @@ __device__ __forceinline__ Proj project_one(const CamCalib& c, float x, float y,
     a = __fmaf_rn(c.k[i][1], cam[1], a);
     pix[i] = __fmaf_rn(c.k[i][2], cam[2], a);
   }
-  // clamp(min=1e-12) keeps NaN like torch does
-  float denom = (pix[2] != pix[2]) ? pix[2] : fmaxf(pix[2], 1e-12f);
-  float u = __fdiv_rn(pix[0], denom);
-  float v = __fdiv_rn(pix[1], denom);
+  Homog h;
+  h.cam_z = cam[2];
+  h.p0 = pix[0];
+  h.p1 = pix[1];
+  h.den = (pix[2] != pix[2]) ? pix[2] : fmaxf(pix[2], 1e-12f);
+  return h;
+}
+
+__device__ __forceinline__ Proj project_finish(const Homog& h, float img_h, float img_w) {
+  const float u = __fdiv_rn(h.p0, h.den);
+  const float v = __fdiv_rn(h.p1, h.den);
   Proj p;
-  p.valid = (cam[2] > 0.f) && (u >= 0.f) && (u < img_w) && (v >= 0.f) && (v < img_h);
+  p.valid = (h.cam_z > 0.f) && (u >= 0.f) && (u < img_w) && (v >= 0.f) && (v < img_h);
   p.u = p.valid ? u : -1.f;
   p.v = p.valid ? v : -1.f;
-  p.z = p.valid ? cam[2] : -1.f;
+  p.z = p.valid ? h.cam_z : -1.f;
   return p;
+}
+
+// Division-free filter: false ONLY when project_finish(h).valid is certainly false, so the two IEEE divisions and the
+// patch arithmetic run for the ~13 % of (point, camera) pairs that can be visible.  With den >= 1e-12 (or NaN):
+//   p0 < -1e-20*den            =>  p0/den <= -0.9e-20, rounds to a negative float              =>  u >= 0 fails
+//   p0 > 1.000001*(W*den)      =>  p0/den > W*(1 + 8e-7) after the two roundings, rounds >= W  =>  u <  W fails
+// Every comparison is false on NaN, so NaN operands are kept for the exact path, which rejects them.
+__device__ __forceinline__ bool maybe_visible(const Homog& h, float img_h, float img_w) {
+  const float lo = __fmul_rn(-1e-20f, h.den);
+  const float hi_u = __fmul_rn(1.000001f, __fmul_rn(img_w, h.den));
+  const float hi_v = __fmul_rn(1.000001f, __fmul_rn(img_h, h.den));
+  const bool out = !(h.cam_z > 0.f) || (h.p0 < lo) || (h.p0 > hi_u) || (h.p1 < lo) || (h.p1 > hi_v);
+  return !out;
+}
+
+__device__ __forceinline__ Proj project_one(const CamCalib& c, float x, float y, float z,
+                                            float img_h, float img_w) {
+  return project_finish(project_homog(c, x, y, z), img_h, img_w);
 }
 
 // (u,v) in original pixels (or -1) -> clamped flat patch index.

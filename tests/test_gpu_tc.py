@@ -113,3 +113,64 @@ def test_fused_full_size_config2(ops):
     # idempotence: a second launch into the same buffers gives identical bits (no stale TMEM / barrier state)
     again = ops.fusion_fwd(pts, K, Rt, hw, sw.encoder, tok, feat, packed)
     assert torch.equal(fused, again)
+
+
+@pytest.mark.parametrize("same", [6, 3])
+def test_fused_overlapping_cameras_and_edge_points(ops, same):
+    """Calibrations in which `same` cameras coincide (points seen by up to six cameras: the general camera mean and the
+    all-cameras projection path of the fused kernel), plus points on image borders, on / behind the image plane and
+    non-finite points.  Records bit-exact against the stand-alone projector; logits against the unfused fp32 route."""
+    B, V = 2, 3001
+    sw = synth.make_sweeps(B, V, "dinov3", seed=77)
+    K, Rt = torch.stack(sw.K).clone(), torch.stack(sw.Rt).clone()
+    K[:, :same] = K[:, :1]
+    Rt[:, :same] = Rt[:, :1]
+    pts = sw.points.clone()
+    hw = sw.image_sizes.float()
+    # points constructed in camera 0's frame and mapped back to the lidar frame: exact borders, the image plane, behind
+    Rinv = torch.linalg.inv(Rt[0, 0].double())
+    k = K[0, 0].double()
+    H, W = float(hw[0, 0]), float(hw[0, 1])
+    special = []
+    for u, v, zc in [(0.0, 0.0, 5.0), (W, 10.0, 5.0), (W - 1e-3, H - 1e-3, 7.0), (10.0, H, 3.0), (-1e-4, 5.0, 2.0),
+                     (W / 2, H / 2, 0.0), (W / 2, H / 2, -4.0), (W / 2, H / 2, 1e-9), (W * (1 + 1e-7), H / 2, 9.0),
+                     (1e-30, 1e-30, 1.0), (W / 2, H * (1 - 1e-7), 60.0)]:
+        cam = torch.tensor([(u - k[0, 2]) / k[0, 0] * zc, (v - k[1, 2]) / k[1, 1] * zc, zc, 1.0], dtype=torch.float64)
+        special.append((Rinv @ cam)[:3].float())
+    n = len(special)
+    pts[0, :n, :3] = torch.stack(special)
+    pts[0, n, :3] = torch.tensor([float("nan"), 1.0, 2.0])
+    pts[0, n + 1, :3] = torch.tensor([float("inf"), 1.0, 2.0])
+    pts[0, n + 2, :3] = torch.tensor([1e30, -1e30, 1e30])
+    pts[0, n + 3, :3] = 0.0
+    w = synth.make_mlp_weights(5)
+    wd = [w[kk].cuda() for kk in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    args = (pts.cuda(), K.cuda(), Rt.cuda(), hw.cuda(), sw.encoder)
+    logits, rec = ops.fusion_fwd(*args, sw.tokens.cuda(), sw.point_feat.cuda(), packed, want_rec=True)
+    ref_rec = ops.project(*args, want_pix=False, want_depth=False, want_valid=False, want_rec=True)["rec"]
+    torch.cuda.synchronize()
+    assert torch.equal(rec, ref_rec)
+    counts = rec.view(torch.uint8).reshape(B, V, 16)[..., 13]
+    assert int(counts.max()) >= same          # the multi-camera paths were really taken
+    ref = ops.mlp_f32(sw.point_feat.cuda(), ops.gather_mean(sw.tokens.cuda(), ref_rec), *wd)
+    assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
+    # and the stand-alone projector agrees with the oracle on these points
+    pix, depth, valid = O.project(pts[..., :3].numpy(), K.numpy(), Rt.numpy(), hw.numpy())
+    assert np.array_equal(valid.astype(np.uint8).sum(1), counts.cpu().numpy())
+
+
+def test_fused_many_sweeps_chunked(ops):
+    """More sweeps than one launch stages calibration for (84 at six cameras): consecutive launches over sweep chunks."""
+    B, V = 100, 333
+    sw = synth.make_sweeps(B, V, "dinov2", seed=9)
+    w = synth.make_mlp_weights(9)
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    args = (sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda(), sw.encoder)
+    tok, feat = sw.tokens.cuda(), sw.point_feat.cuda()
+    logits, rec = ops.fusion_fwd(*args, tok, feat, packed, want_rec=True)
+    ref_rec = ops.project(*args, want_pix=False, want_depth=False, want_valid=False, want_rec=True)["rec"]
+    assert torch.equal(rec, ref_rec)
+    ref = ops.mlp_f32(feat, ops.gather_mean(tok, ref_rec), *wd)
+    assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
