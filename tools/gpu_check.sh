@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, bench, experiment harness, ncu launch list + one full capture of the fused kernel.
+# One GPU-box visit: parity tests, bench, experiment harness, ncu launch list (the full capture is tools/gpu_ncu.sh: one ncu per box visit).
 set -x
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt
@@ -12,6 +12,4 @@ TDSSF_LIB=$PWD/3d-semantic-segmentation-fusion_b200/build/variants/TDSSF_PROFILE
 cat gpurun_out/exp_default.json; tail -30 gpurun_out/exp_profile.err
 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:fused_mlp -s 3 -c 2 -o gpurun_out/prof_fused python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 ls -la gpurun_out
