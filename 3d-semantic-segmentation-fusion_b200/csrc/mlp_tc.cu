@@ -137,10 +137,15 @@ struct Params {
 #define TRACE(dbg, ev, it)
 #endif
 
+#ifdef TDSSF_SPIN
+#define TDSSF_WAIT_PROBE ptx::mbar_test_wait   // busy polling: reacts within a few tens of cycles
+#else
+#define TDSSF_WAIT_PROBE ptx::mbar_try_wait    // suspends the warp until the phase completes (or the time hint expires)
+#endif
 __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* debug, int code) {
-  if (ptx::mbar_try_wait(bar, parity)) return;
+  if (TDSSF_WAIT_PROBE(bar, parity)) return;
   const long long t0 = clock64();
-  while (!ptx::mbar_try_wait(bar, parity)) {
+  while (!TDSSF_WAIT_PROBE(bar, parity)) {
     if (clock64() - t0 > 4000000000LL) {  // ~2 s: a protocol bug, never a legitimate wait
       if (debug) atomicExch(debug, (unsigned)code | 0x80000000u);
       __trap();
@@ -148,6 +153,25 @@ __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned
   }
 #ifdef TDSSF_PROFILE
   PROF_ADD(debug, code, t0);
+#endif
+}
+
+// busy-polling wait for the single MMA-issuing threads: reacts within a few tens of cycles
+__device__ __forceinline__ void wait_bar_poll(uint32_t bar, uint32_t parity, unsigned int* debug, int code) {
+#ifdef TDSSF_MMA_SLEEPS
+  wait_bar(bar, parity, debug, code);
+#else
+  if (ptx::mbar_test_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!ptx::mbar_test_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      if (debug) atomicExch(debug, (unsigned)code | 0x80000000u);
+      __trap();
+    }
+  }
+#ifdef TDSSF_PROFILE
+  PROF_ADD(debug, code, t0);
+#endif
 #endif
 }
 
@@ -628,6 +652,7 @@ fused_mlp_kernel(const Params p) {
       wait_bar(bar(kBarAcc1Full + buf), par, p.debug, 7);
       ptx::tc_fence_after();
       if (warp == 0) TRACE(p.debug, 4, it);
+#ifndef TDSSF_EXP_NOEPI  // (timing experiment: the epilogue only runs the barrier protocol)
       {
         uint32_t va[16], vb[16], h[8];
         const uint32_t src = tb + ch * 128;
@@ -645,6 +670,7 @@ fused_mlp_kernel(const Params p) {
           ptx::tmem_st8(src + (c + 1) * 8, h);
         }
       }
+#endif
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
@@ -655,6 +681,7 @@ fused_mlp_kernel(const Params p) {
       wait_bar(bar(kBarAcc2Full + buf), par, p.debug, 8);
       ptx::tc_fence_after();
       if (warp == 0) TRACE(p.debug, 6, it);
+#ifndef TDSSF_EXP_NOEPI
       {
         uint32_t va[16], vb[16], h[8];
         const uint32_t src = tb + 64 + ch * 32, dst = tb + 192 + ch * 16;
@@ -667,6 +694,7 @@ fused_mlp_kernel(const Params p) {
         act16(vb, bias + 16, h);
         ptx::tmem_st8(dst + 8, h);
       }
+#endif
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
@@ -699,110 +727,86 @@ fused_mlp_kernel(const Params p) {
     }
   } else if (warp < kProdWarp0) {
     if (kRegsAux < 96) ptx::setmaxnreg_dec<kRegsAux>(); else ptx::setmaxnreg_inc<kRegsAux>();
+    constexpr uint32_t kI1 = ptx::idesc_bf16(256, kN1), kI2 = ptx::idesc_bf16(256, kN2), kI3 = ptx::idesc_bf16(256, kN3);
     if (warp == kMmaWarp) {
-      // =============================== weights + MMA issue ==========================================
+      // =============================== weights + layer-1 MMA issue ===================================
+      // tcgen05.mma issue is paced by the tensor pipe (the issuing thread blocks while the previous MMA starts), so the
+      // pipe is busy only while this thread has the next MMA at hand: its loop is kept to wait - 4 MMAs - commit, and
+      // the small layers of the previous tile are issued by another thread (warp kMmaWarp + 1).
       if (leader && lane == 0 && n_iters > 0) {
         // B operands are read from both CTAs' shared memory: wait for our image and for the peer's
         wait_bar(bar(kBarWFull), 0, p.debug, 1);
         wait_bar(bar(kBarPeerW), 0, p.debug, 11);
-        constexpr uint32_t kI1 = ptx::idesc_bf16(256, kN1), kI2 = ptx::idesc_bf16(256, kN2), kI3 = ptx::idesc_bf16(256, kN3);
-        // Event-driven issue: the layer-1 MMAs of tile t are issued slab by slab as the producers deliver them; while
-        // waiting, the thread services tile t-1, issuing its layer-2 MMAs as soon as the epilogue has written H1 and its
-        // layer-3 MMAs as soon as H2 is there, so that the small layers never wait behind a slow producer.
-        int pend = -1;          // tile whose layer 2 / layer 3 is still to be issued
-        bool need2 = false, need3 = false;
-        auto service = [&]() {
-          if (pend < 0) return;
-          const uint32_t buf = pend & 1, par = (pend >> 1) & 1, tb = tmem + buf * 256;
-          if (need2 && ptx::mbar_test_wait(bar(kBarH1Full + buf), par)) {
-            ptx::tc_fence_after();
-            TRACE(p.debug, 2, pend);
-            // layer 2: A = H1 (TMEM cols [0,64) and [128,192) of the buffer), B = W2, D = cols [64,128)
-#pragma unroll
-            for (int k = 0; k < kN1 / 16; ++k) {
-              const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
-              ptx::umma_ts_2cta(tb + 64, tb + (k < 8 ? k * 8 : 128 + (k - 8) * 8), bd, kI2, k != 0);
-            }
-            ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
-            need2 = false;
-          }
-          if (!need2 && need3 && ptx::mbar_test_wait(bar(kBarH2Full + buf), par)) {
-            ptx::tc_fence_after();
-            TRACE(p.debug, 3, pend);
-            // layer 3: A = H2 (cols [192,224)), B = W3, D = cols [224,256)
-#pragma unroll
-            for (int k = 0; k < kN2 / 16; ++k) {
-              const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
-              ptx::umma_ts_2cta(tb + 224, tb + 192 + k * 8, bd, kI3, k != 0);
-            }
-            ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
-            need3 = false;
-            pend = -1;
-          }
-        };
-        // wait on `b` while servicing the pending tile; ~2 s without progress is a protocol bug
-        auto wait_serving = [&](uint32_t b, uint32_t parity, int code) {
-          if (ptx::mbar_test_wait(b, parity)) return;
-          const long long t0 = clock64();
-          while (!ptx::mbar_test_wait(b, parity)) {
-            service();
-            if (clock64() - t0 > 4000000000LL) {
-              if (p.debug) atomicExch(p.debug, (unsigned)code | 0x80000000u);
-              __trap();
-            }
-          }
-          PROF_ADD(p.debug, code, t0);
-        };
         uint32_t stage = 0, phase = 0;  // A ring cursor
         for (int it = 0; it < n_iters; ++it) {
           const uint32_t buf = it & 1;
-          if (it >= 2) wait_serving(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, 2);
+          if (it >= 2) wait_bar_poll(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, p.debug, 2);
           ptx::tc_fence_after();
           TRACE(p.debug, 0, it);
 #pragma unroll 1
           for (int s = 0; s < kSlabs1; ++s) {
-            wait_serving(bar(kBarAFull + stage), phase, 3);
+            wait_bar_poll(bar(kBarAFull + stage), phase, p.debug, 3);
             ptx::tc_fence_after();
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t ad = ptx::smem_desc_sw128(sbase + kOffRing + stage * kASlab + kk * 32);
               const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW1 + s * kW1Slab + kk * 32);
+#ifndef TDSSF_EXP_NOMMA  // (timing experiment: layer 1 not issued)
               ptx::umma_ss_2cta(tmem + buf * 256, ad, bd, kI1, (s | kk) != 0);
+#else
+              (void)ad; (void)bd;
+#endif
             }
             ptx::umma_commit_2cta(bar(kBarAEmpty + stage), 3);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
-            service();
           }
           ptx::umma_commit_2cta(bar(kBarAcc1Full + buf), 3);
           TRACE(p.debug, 1, it);
-          // the previous tile must have its small layers issued before this one becomes the pending tile
-          if (pend >= 0) {
-            const long long t0 = clock64();
-            while (pend >= 0) {
-              service();
-              if (clock64() - t0 > 4000000000LL) {
-                if (p.debug) atomicExch(p.debug, 4u | 0x80000000u);
-                __trap();
-              }
-            }
-            PROF_ADD(p.debug, 4, t0);
-          }
-          pend = it; need2 = true; need3 = true;
-        }
-        {
-          const long long t0 = clock64();
-          while (pend >= 0) {
-            service();
-            if (clock64() - t0 > 4000000000LL) {
-              if (p.debug) atomicExch(p.debug, 5u | 0x80000000u);
-              __trap();
-            }
-          }
         }
       }
       if (!leader && lane == 0) {
         wait_bar(bar(kBarWFull), 0, p.debug, 6);
         ptx::mbar_arrive_cluster(ptx::mapa(bar(kBarPeerW), 0));
+      }
+      __syncwarp();
+    } else if (warp == kMmaWarp + 1) {
+      // =============================== layer-2 / layer-3 MMA issue ===================================
+      // A operands are the bf16 activations the epilogue wrote into TMEM; issued as soon as they are complete, from a
+      // thread of its own so that they never wait behind (or delay) the layer-1 stream of the next tile.
+      if (leader && lane == 0 && n_iters > 0) {
+        wait_bar(bar(kBarWFull), 0, p.debug, 1);
+        wait_bar(bar(kBarPeerW), 0, p.debug, 11);
+        for (int it = 0; it < n_iters; ++it) {
+          const uint32_t buf = it & 1, par = (it >> 1) & 1, tb = tmem + buf * 256;
+          wait_bar_poll(bar(kBarH1Full + buf), par, p.debug, 4);
+          ptx::tc_fence_after();
+          TRACE(p.debug, 2, it);
+          // layer 2: A = H1 (TMEM cols [0,64) and [128,192) of the buffer), B = W2, D = cols [64,128)
+#pragma unroll
+          for (int k = 0; k < kN1 / 16; ++k) {
+            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
+#ifndef TDSSF_EXP_NOL23  // (timing experiment: layers 2 and 3 not issued)
+            ptx::umma_ts_2cta(tb + 64, tb + (k < 8 ? k * 8 : 128 + (k - 8) * 8), bd, kI2, k != 0);
+#else
+            (void)bd;
+#endif
+          }
+          ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
+          wait_bar_poll(bar(kBarH2Full + buf), par, p.debug, 5);
+          ptx::tc_fence_after();
+          TRACE(p.debug, 3, it);
+          // layer 3: A = H2 (cols [192,224)), B = W3, D = cols [224,256)
+#pragma unroll
+          for (int k = 0; k < kN2 / 16; ++k) {
+            const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
+#ifndef TDSSF_EXP_NOL23
+            ptx::umma_ts_2cta(tb + 224, tb + 192 + k * 8, bd, kI3, k != 0);
+#else
+            (void)bd;
+#endif
+          }
+          ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
+        }
       }
       __syncwarp();
     }
@@ -852,6 +856,9 @@ fused_mlp_kernel(const Params p) {
 
     auto issue = [&](auto S_, int it, Set& n) {
       constexpr int S = decltype(S_)::value;
+#ifdef TDSSF_EXP_NOPROD  // (timing experiment: the producers only run the barrier protocol)
+      return;
+#endif
       const int64_t row0 = tile_row0(it) + pw * kRowsPerWarp;
       if (S == 0) {  // point features
 #pragma unroll
@@ -891,6 +898,7 @@ fused_mlp_kernel(const Params p) {
       if (S == 0 && pw == 0) TRACE(p.debug, 10, it);
       wait_bar(bar(kBarAEmpty + stage), phase ^ 1, p.debug, 10);
       const uint32_t slab_off = stage * kASlab;
+#ifndef TDSSF_EXP_NOPROD
 #pragma unroll
       for (int st = 0; st < kSteps; ++st) {
         float acc[8];
@@ -904,6 +912,9 @@ fused_mlp_kernel(const Params p) {
                       pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
         }
       }
+#else
+      (void)slab_off;
+#endif
       ptx::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
