@@ -747,6 +747,7 @@ fused_mlp_kernel(const Params p) {
           for (int s = 0; s < kSlabs1; ++s) {
             wait_bar_poll(bar(kBarAFull + stage), phase, p.debug, 3);
             ptx::tc_fence_after();
+            if (it >= 4 && it < 8) TRACE(p.debug, 11, 1 + (it - 4) * 7 + s);   // slab trace: slab seen full
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t ad = ptx::smem_desc_sw128(sbase + kOffRing + stage * kASlab + kk * 32);
@@ -758,6 +759,7 @@ fused_mlp_kernel(const Params p) {
 #endif
             }
             ptx::umma_commit_2cta(bar(kBarAEmpty + stage), 3);
+            if (it >= 4 && it < 8) TRACE(p.debug, 12, 1 + (it - 4) * 7 + s);   // its MMAs and commit issued
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
           ptx::umma_commit_2cta(bar(kBarAcc1Full + buf), 3);
@@ -854,28 +856,16 @@ fused_mlp_kernel(const Params p) {
 
     struct Set { Raw8 a[kSteps]; };
 
-    auto issue = [&](auto S_, int it, Set& n) {
+    // loads of slab S of tile `it`: setup once per slab, then one step (= one row of the quarter-warp) at a time
+    auto issue_setup = [&](auto S_, int it) {
       constexpr int S = decltype(S_)::value;
-#ifdef TDSSF_EXP_NOPROD  // (timing experiment: the producers only run the barrier protocol)
-      return;
-#endif
-      const int64_t row0 = tile_row0(it) + pw * kRowsPerWarp;
-      if (S == 0) {  // point features
-#pragma unroll
-        for (int st = 0; st < kSteps; ++st) {
-          const int64_t row = row0 + row_of(st, quarter);
-          const char* px = row < p.N ? reinterpret_cast<const char*>(p.x_pt) + row * (kCp * 4) + ql * 16 : zero_row;
-          n.a[st].lo = ldg16c(px);
-          n.a[st].hi = ldg16c(px + 128);
-        }
-        return;
-      }
       if (S == 1) {  // the tile's row sources
         if (kGather) {
 #pragma unroll
           for (int st = 0; st < kSteps; ++st) pa[st] = pn[st] + ql * 16;
           load_sources(it + 1);
         } else {
+          const int64_t row0 = tile_row0(it) + pw * kRowsPerWarp;
 #pragma unroll
           for (int st = 0; st < kSteps; ++st) {
             const int64_t row = row0 + row_of(st, quarter);
@@ -883,44 +873,76 @@ fused_mlp_kernel(const Params p) {
           }
         }
       }
-      constexpr int kOff = (S - 1) * (kTok32 ? 256 : kPieceBytes);
-#pragma unroll
-      for (int st = 0; st < kSteps; ++st) {
-        n.a[st].lo = ldg16c(pa[st] + kOff);
-        if (kTok32) n.a[st].hi = ldg16c(pa[st] + kOff + 128);
+    };
+    auto issue_one = [&](auto S_, int it, int st, Set& n) {
+      constexpr int S = decltype(S_)::value;
+#ifdef TDSSF_EXP_NOPROD  // (timing experiment: the producers only run the barrier protocol)
+      return;
+#endif
+      if (S == 0) {  // point features
+        const int64_t row = tile_row0(it) + pw * kRowsPerWarp + row_of(st, quarter);
+        const char* px = row < p.N ? reinterpret_cast<const char*>(p.x_pt) + row * (kCp * 4) + ql * 16 : zero_row;
+        n.a[st].lo = ldg16c(px);
+        n.a[st].hi = ldg16c(px + 128);
+        return;
       }
+      constexpr int kOff = (S - 1) * (kTok32 ? 256 : kPieceBytes);
+      n.a[st].lo = ldg16c(pa[st] + kOff);
+      if (kTok32) n.a[st].hi = ldg16c(pa[st] + kOff + 128);
+    };
+    auto issue = [&](auto S_, int it, Set& n) {
+      issue_setup(S_, it);
+#pragma unroll
+      for (int st = 0; st < kSteps; ++st) issue_one(S_, it, st, n);
     };
 
     uint32_t stage = 0, phase = 0;  // A ring cursor
-    auto consume = [&](auto S_, int it, const Set& c) {
+    // conversion + store of one step of slab S out of set c into ring slot `stage`
+    auto consume_one = [&](auto S_, int st, const Set& c, uint32_t slab_off) {
       constexpr int S = decltype(S_)::value;
       constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
-      if (S == 0 && pw == 0) TRACE(p.debug, 10, it);
-      wait_bar(bar(kBarAEmpty + stage), phase ^ 1, p.debug, 10);
-      const uint32_t slab_off = stage * kASlab;
-#ifndef TDSSF_EXP_NOPROD
-#pragma unroll
-      for (int st = 0; st < kSteps; ++st) {
-        float acc[8];
-        if (kF32) {
-          raw8_f32_to_f8(c.a[st], acc);
-          ptx::sts64(so_lo[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]));
-          ptx::sts64(so_hi[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
-        } else {
-          TokRaw<TokT>::to_f8(c.a[st], acc);
-          ptx::sts128(so_16[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
-                      pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
-        }
-      }
-#else
+#ifdef TDSSF_EXP_NOPROD
       (void)slab_off;
+      return;
 #endif
+      float acc[8];
+      if (kF32) {
+        raw8_f32_to_f8(c.a[st], acc);
+        ptx::sts64(so_lo[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]));
+        ptx::sts64(so_hi[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+      } else {
+        TokRaw<TokT>::to_f8(c.a[st], acc);
+        ptx::sts128(so_16[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
+                    pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+      }
+    };
+    // One pipeline step: the loads of slab S2 of tile it2 go into set `nxt` (all eight of the thread at once, before
+    // anything can block), then slab S of tile `it` leaves set `cur` for the ring.  (Measured: alternating loads and
+    // stores row by row, or issuing the loads after the wait for the ring slot, is 2-5 % slower.)
+    auto step_fused = [&](auto S_, int it, const Set& cur, auto S2_, int it2, Set& nxt) {
+      constexpr int S = decltype(S_)::value;
+      if (it2 < n_iters) issue(S2_, it2, nxt);
+#ifdef TDSSF_XPT_PREFETCH  // (experiment) the next tile's point features, one contiguous 32 KB block, towards L2
+      if (S == 2 && pw == 0 && lane == 0 && it + 1 < n_iters) {
+        const int64_t r0 = tile_row0(it + 1);
+        if (r0 + kTileM <= p.N)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.x_pt + r0 * kCp), "r"(kTileM * kCp * 4) : "memory");
+      }
+#endif
+      if (S == 0 && pw == 0) TRACE(p.debug, 10, it);
+      if (pw == 0 && it >= 4 && it < 8) TRACE(p.debug, 13, (it - 4) * 7 + S);   // slab trace: loads issued
+      wait_bar(bar(kBarAEmpty + stage), phase ^ 1, p.debug, 10);
+      if (pw == 0 && it >= 4 && it < 8) TRACE(p.debug, 14, (it - 4) * 7 + S);   // ring slot free
+      const uint32_t slab_off = stage * kASlab;
+#pragma unroll
+      for (int st = 0; st < kSteps; ++st) consume_one(S_, st, cur, slab_off);
       ptx::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
         ptx::mbar_arrive_cluster(leader_full0 + 8 * stage);
       }
       __syncwarp();
+      if (pw == 0 && it >= 4 && it < 8) TRACE(p.debug, 15, (it - 4) * 7 + S);   // slab written and announced
       if (++stage == kStages) { stage = 0; phase ^= 1; }
     };
 
@@ -933,8 +955,7 @@ fused_mlp_kernel(const Params p) {
       constexpr int S = decltype(S_)::value;
       constexpr int S2 = (S + 2) % kSlabs1;
       const int it2 = it + (S + 2 >= kSlabs1 ? 1 : 0);
-      if (it2 < n_iters) issue(std::integral_constant<int, S2>{}, it2, nxt2);
-      consume(S_, it, cur);
+      step_fused(S_, it, cur, std::integral_constant<int, S2>{}, it2, nxt2);
     };
     auto tile = [&](int it, Set& x, Set& y, Set& z) {  // slab 0 in x, slab 1 in y
       step(std::integral_constant<int, 0>{}, it, x, z);
@@ -961,8 +982,7 @@ fused_mlp_kernel(const Params p) {
       constexpr int S = decltype(S_)::value;
       constexpr int S1 = (S + 1) % kSlabs1;
       const int it1 = it + (S + 1 >= kSlabs1 ? 1 : 0);
-      if (it1 < n_iters) issue(std::integral_constant<int, S1>{}, it1, nxt);
-      consume(S_, it, cur);
+      step_fused(S_, it, cur, std::integral_constant<int, S1>{}, it1, nxt);
     };
     auto tile = [&](int it, Set& x, Set& y) {  // slab 0 in x
       step(std::integral_constant<int, 0>{}, it, x, y);
@@ -1071,11 +1091,20 @@ static int launch(const Params& p, cudaStream_t s) {
       fprintf(stderr, "  prologue %lld cycles; first L1 start %lld, last acc free %lld cycles after the prologue start (%d tiles)\n",
               (long long)(tr[12 * 32] - tr[11 * 32]), (long long)(tr[0] - tr[11 * 32]),
               (long long)(tr[9 * 32 + (p.n_pairs / clusters) - 1] - tr[11 * 32]), p.n_pairs / clusters);
+      {
+        const unsigned long long s0 = tr[13 * 32];
+        fprintf(stderr, "  slab trace, tiles 4-7 of cluster 5 rank 0 (producer warp 0 / MMA thread), cycles from the first entry\n"
+                        "  slab   prod:loads-awaited  slot-free  announced |  mma:seen-full  issued\n");
+        for (int i = 0; i < 28; ++i)
+          fprintf(stderr, "  %d.%d %18lld %10lld %10lld | %14lld %7lld\n", 4 + i / 7, i % 7, (long long)(tr[13 * 32 + i] - s0),
+                  (long long)(tr[14 * 32 + i] - s0), (long long)(tr[15 * 32 + i] - s0), (long long)(tr[11 * 32 + 1 + i] - s0),
+                  (long long)(tr[12 * 32 + 1 + i] - s0));
+      }
       const unsigned long long t0 = tr[0 * 32 + 4];
       fprintf(stderr, "  timeline of cluster 5 rank 0, cycles relative to 'mma L1 start' of tile 4\n  %-16s", "event");
       for (int it = 4; it < 10; ++it) fprintf(stderr, " %9d", it);
       fprintf(stderr, "\n");
-      for (int e = 0; e < 16; ++e) {
+      for (int e = 0; e < 11; ++e) {
         fprintf(stderr, "  %-16s", ev[e]);
         for (int it = 4; it < 10; ++it) fprintf(stderr, " %9lld", (long long)(tr[e * 32 + it] - t0));
         fprintf(stderr, "\n");
