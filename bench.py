@@ -167,12 +167,14 @@ def run_reference_arm(args, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "sweeps_per_step": n, "points_per_sweep": vs, "device": "host CPU"},
+        "config": {"workload": desc, "sweeps_per_gpu": B, "points_per_sweep": V, "tokens": "fp32",
+                   "mlp": "fp32 ATen ops on the host cores", "sample_per_step": f"{n} sweeps x {vs} pts",
+                   "parallelism": "host CPU, rank 0 only"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -304,7 +306,7 @@ def run_own_arm(args, rank, world, local_rank):
                 "api": "utils.fusion_model.FeatureFusionModel.forward (drop-in), pinned host inputs, logits copied to host"},
         "gpu_launches": args.steps, "clocks": clocks,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -312,6 +314,27 @@ def run_own_arm(args, rank, world, local_rank):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused kernel, from the ncu --set full capture
 # under profiles/ (None until captured)
 TRAFFIC_BYTES = {"config2": 293_600_000}  # profiles/r1_ncu_fused_v5_summary.txt: 250.3 MB read + 43.3 MB written
+
+
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Libraries (NCCL's version banner, for one) write to fd 1; the contract is ONE JSON line on stdout.  Everything
+    written to fd 1 from here on goes to stderr, and emit() writes the line to the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -323,6 +346,7 @@ def main():
     ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    _quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -1,0 +1,194 @@
+"""Per-row timings of the hot path on one GPU: every stand-alone kernel with its algorithmic bytes or
+FLOPs against the measured peaks, and the two composite steps BASELINE's configs[2] (training fwd/bwd per GPU: 4 sweeps)
+and configs[4] (evaluation step) describe.  CUDA events, 3 warm-up + `--iters` timed calls, inputs larger than L2 where
+the row's working set allows it.  One JSON object per line; `python tools/bench_rows.py > profiles/rN_rows.jsonl`."""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "3d-semantic-segmentation-fusion_b200")]
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+from tdssf import ops, synth  # noqa: E402
+from utils.fusion_model import FeatureFusionModel  # noqa: E402
+from utils.losses import CELSLoss  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--iters", type=int, default=20)
+a = ap.parse_args()
+peaks, peak_kind = bench.measured_peaks()
+HBM = peaks["hbm_gbs"]
+FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # CUDA-core FMA peak at the maximum SM clock (no measured figure)
+dev = torch.device("cuda")
+
+
+def timeit(fn, n=a.iters):
+    for _ in range(3):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def emit(row, kernel, ms, n_units, unit, bytes_per_unit=None, flops_per_unit=None, note=""):
+    out = {"row": row, "kernel": kernel, "ms": round(ms, 5), "units": n_units, "unit": unit,
+           "throughput": n_units / (ms * 1e-3), "note": note}
+    if bytes_per_unit is not None:
+        gbs = bytes_per_unit * n_units / (ms * 1e-3) / 1e9
+        out.update(bound="hbm", algorithmic_bytes_per_unit=bytes_per_unit, achieved_gbs=gbs, peak_gbs=HBM, frac=gbs / HBM)
+    if flops_per_unit is not None:
+        tf = flops_per_unit * n_units / (ms * 1e-3) / 1e12
+        out.update(bound="fp32 fma", flops_per_unit=flops_per_unit, achieved_tflops=tf, peak_tflops=FP32_TFLOPS,
+                   frac=tf / FP32_TFLOPS)
+    print(json.dumps(out), flush=True)
+
+
+# ---------------------------------------------------------------- config 2 shapes: 8 sweeps x 34 720 points -----
+B, V = 8, 34720
+sw = synth.make_sweeps(B, V, "dinov3", seed=2000)
+enc = sw.encoder
+M = enc.n_patches
+w = synth.make_mlp_weights(0)
+wd = [w[k].to(dev) for k in bench.W_KEYS]
+pts, K, Rt = sw.points.to(dev), torch.stack(sw.K).to(dev), torch.stack(sw.Rt).to(dev)
+hw, tok, feat = sw.image_sizes.float().to(dev), sw.tokens.to(dev), sw.point_feat.to(dev)
+N = B * V
+
+# a1-a3 projection
+ms = timeit(lambda: ops.project(pts, K, Rt, hw, enc, want_pix=False, want_depth=False, want_valid=False, want_rec=True))
+emit("a1-a3", "project_kernel (records only)", ms, N, "points", bytes_per_unit=16 + 16,
+     note="16 B point in, 16 B camera record out; 6 cameras x (27 flops + 4 IEEE divisions) per point")
+ms = timeit(lambda: ops.project(pts, K, Rt, hw, enc, want_flat=True, want_rec=True))
+emit("a1-a3", "project_kernel (all reference outputs)", ms, N, "points", bytes_per_unit=16 + 6 * (8 + 4 + 1 + 4) + 16,
+     note="pix (B,6,V,2) + depth + valid + flat index + record")
+rec = ops.project(pts, K, Rt, hw, enc, want_pix=False, want_depth=False, want_valid=False, want_rec=True)["rec"]
+
+# a4-a5 gather + masked camera mean (stand-alone)
+ms = timeit(lambda: ops.gather_mean(tok, rec))
+emit("a4-a5", "gather_mean_kernel<float>", ms, N, "points", bytes_per_unit=16 + 6 * M * 1536 / V + 1536,
+     note="record in, token maps read once, 1536 B fp32 feature out (the fused kernel never writes this)")
+img = ops.gather_mean(tok, rec)
+
+# a6 MLP, fp32 CUDA-core kernels (1e-5 parity mode, training)
+flops = 2 * (448 * 256 + 256 * 64 + 64 * 16)
+ms = timeit(lambda: ops.mlp_f32(feat, img, *wd), n=5)
+emit("a6", "mlp_fwd_f32", ms, N, "points", flops_per_unit=flops, note="fp32 FMA, inference call (no saved activations)")
+wg = [t.clone().requires_grad_(True) for t in wd]
+featg = feat.clone().requires_grad_(True)
+
+
+def mlp_train():
+    out = ops.mlp_f32(featg, img, *wg)
+    out.backward(torch.ones_like(out))
+    for t in wg:
+        t.grad = None
+    featg.grad = None
+
+
+ms = timeit(mlp_train, n=5)
+emit("a6", "mlp_fwd_f32 + mlp_bwd_f32", ms, N, "points", flops_per_unit=3 * flops - 2 * 384 * 256,
+     note="forward with saved h1/h2 + backward (dW, db, dx_pt; no gradient to the image feature)")
+
+# a6 on the tensor cores (dense features) and a1-a6 fused
+packed = ops.pack_weights(*wd)
+ms = timeit(lambda: ops.mlp_tc(feat, img, packed))
+emit("a6", "fused_mlp_kernel<float,false> (dense features)", ms, N, "points", bytes_per_unit=4 * 448 + 64,
+     note="tcgen05 bf16 MLP fed by a dense fp32 [N,384] feature")
+out = torch.empty((B, V, 16), device=dev)
+ms = timeit(lambda: ops.fusion_fwd(pts, K, Rt, hw, enc, tok, feat, packed, out=out))
+emit("a1-a6", "fused_mlp_kernel<float,true>", ms, N, "points", bytes_per_unit=bench.algorithmic_bytes_per_point(V, M),
+     note="the bench.py kernel, for reference")
+
+# ---------------------------------------------------------------- a7 devoxelize ---------------------------------
+Bd, P, Vd = 2, 34720, 30000
+gen = torch.Generator().manual_seed(5)
+raw = synth.make_points(Bd, P, gen)[..., :3].contiguous().to(dev)
+vox = (raw[:, torch.randperm(P, generator=gen)[:Vd]] + 0.05).contiguous()
+ms = timeit(lambda: ops.devox_nn(raw, vox), n=5)
+emit("a7", "devox_nn_kernel", ms, Bd * P * Vd, "point-voxel pairs", flops_per_unit=8,
+     note=f"{Bd} sweeps x {P} points x {Vd} voxels, expanded-form distance + running arg-min (~8 flops per pair); "
+          "the reference materialises a P x V_max matrix")
+idx = ops.devox_nn(raw, vox)
+scores = torch.randn(Bd, Vd, 16, device=dev)
+ms = timeit(lambda: ops.devox_gather(scores, idx))
+emit("a7", "devox_gather_kernel", ms, Bd * P, "points", bytes_per_unit=8 + 64 + 64, note="index + 16 logits in (L2) + 16 out")
+
+# ---------------------------------------------------------------- a8-a10 CE + Lovasz ----------------------------
+Bl = 4
+logits = torch.randn(Bl, V, 16, device=dev)
+labels = synth.make_labels(Bl, V, gen).to(dev)
+mask = torch.ones(Bl, V, dtype=torch.bool, device=dev)
+cw = torch.ones(16, device=dev)
+lg = logits.clone().requires_grad_(True)
+
+
+def cels_step():
+    total = ops.cels(lg, labels, mask, cw)[0]
+    total.backward()
+    lg.grad = None
+
+
+ms = timeit(cels_step, n=10)
+emit("a8-a10", "cels_fwd_bwd (all kernels, incl. the host read of n_valid)", ms, Bl * V, "points",
+     bytes_per_unit=64 + 8 + 1 + 64 + 16 * (4 * 12 * 2),
+     note="logits + labels + mask in, dlogits out, and per class 4 radix passes reading and writing a 12-byte key/payload")
+
+# ---------------------------------------------------------------- a11 confusion matrix --------------------------
+n_cm = 8 * 34720
+pr = torch.randint(1, 17, (n_cm,), device=dev)
+lb = torch.randint(1, 17, (n_cm,), device=dev)
+cm = torch.zeros(16, 16, dtype=torch.int64, device=dev)
+ms = timeit(lambda: ops.confusion(pr, lb, 16, out=cm))
+emit("a11", "confusion_kernel", ms, n_cm, "points", bytes_per_unit=16, note="two int64 per point; 4.4 MB: L2-resident after warm-up")
+
+# ---------------------------------------------------------------- composite steps -------------------------------
+class Pcd(torch.nn.Module):
+    def devoxelize(self, s):
+        return s, None
+
+
+# configs[2]: training fwd/bwd, 4 sweeps per GPU (batch 32 over 8 GPUs), fp32 kernels (a gradient is required)
+Bt = 4
+model = FeatureFusionModel(enc, Pcd(), 64, 384, 16, device=dev).to(dev)
+model.load_state_dict(w, strict=True)
+crit = CELSLoss()
+t_tok, t_feat, t_pts = tok[:Bt], feat[:Bt].clone().requires_grad_(True), pts[:Bt]
+t_hw, t_K, t_Rt = sw.image_sizes[:Bt], sw.K[:Bt], sw.Rt[:Bt]
+t_lab, t_mask = labels[:Bt], mask[:Bt]
+
+
+def train_step():
+    scores = model(t_tok, t_feat, t_pts, None, t_hw, t_K, t_Rt)
+    total = crit(scores, t_lab, t_mask)[0]
+    total.backward()
+    model.zero_grad(set_to_none=True)
+    t_feat.grad = None
+
+
+ms = timeit(train_step, n=5)
+emit("config3", "training step per GPU (drop-in modules: forward + CE/Lovasz + backward)", ms, Bt * V, "points",
+     note="4 sweeps x 34 720 points; project + gather + fp32 MLP fwd, cels fwd/bwd, fp32 MLP bwd; no optimizer, no all-reduce")
+
+# configs[4]: evaluation step: fused inference + argmax + confusion accumulation (8 sweeps)
+cm.zero_()
+lab8 = torch.randint(1, 17, (B, V), device=dev)
+
+
+def eval_step():
+    with torch.no_grad():
+        s = ops.fusion_fwd(pts, K, Rt, hw, enc, tok, feat, packed, out=out)
+        pred = s.argmax(-1) + 1
+        ops.confusion(pred, lab8, 16, out=cm)
+
+
+ms = timeit(eval_step)
+emit("config5", "evaluation step per GPU (fused forward + argmax + confusion)", ms, N, "points",
+     note="8 sweeps x 34 720 points; torch argmax between the two kernels")
