@@ -876,7 +876,7 @@ fused_mlp_kernel(const Params p) {
     };
     auto issue_one = [&](auto S_, int it, int st, Set& n) {
       constexpr int S = decltype(S_)::value;
-#ifdef TDSSF_EXP_NOPROD  // (timing experiment: the producers only run the barrier protocol)
+#if defined(TDSSF_EXP_NOPROD) || defined(TDSSF_EXP_NOLOAD)  // (timing experiments: no global loads)
       return;
 #endif
       if (S == 0) {  // point features
@@ -901,7 +901,7 @@ fused_mlp_kernel(const Params p) {
     auto consume_one = [&](auto S_, int st, const Set& c, uint32_t slab_off) {
       constexpr int S = decltype(S_)::value;
       constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
-#ifdef TDSSF_EXP_NOPROD
+#if defined(TDSSF_EXP_NOPROD) || defined(TDSSF_EXP_NOSTORE)  // (timing experiments: no conversion, no stores)
       (void)slab_off;
       return;
 #endif

@@ -313,7 +313,7 @@ def run_own_arm(args, rank, world, local_rank):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused kernel, from the ncu --set full capture
 # under profiles/ (None until captured)
-TRAFFIC_BYTES = {"config2": 293_600_000}  # profiles/r1_ncu_fused_v5_summary.txt: 250.3 MB read + 43.3 MB written
+TRAFFIC_BYTES = {"config2": 291_800_000}  # profiles/r1_ncu_fused_v7_summary.txt: 249.9 MB read + 41.9 MB written
 
 
 _REAL_STDOUT = None
