@@ -248,15 +248,28 @@ def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=Fa
 # ------------------------------------------------------------------------------------------------
 # a7
 # ------------------------------------------------------------------------------------------------
-def devox_nn(pts: torch.Tensor, vox: torch.Tensor) -> torch.Tensor:
-    """pts (B,P,>=3), vox (B,V,>=3) CUDA fp32 -> (B,P) int64 nearest-voxel indices."""
+_devox_ws: dict = {}
+
+
+def devox_nn(pts: torch.Tensor, vox: torch.Tensor, cell: Optional[float] = 0.25) -> torch.Tensor:
+    """pts (B,P,>=3), vox (B,V,>=3) CUDA fp32 -> (B,P) int64 nearest-voxel indices (first index on ties).
+    `cell`: edge of the search grid's cells in coordinate units (any positive value gives the same indices);
+    None = brute force over all P x V pairs."""
     _need_cuda(pts, vox)
     pts = _f32c(pts)
     vox = _f32c(vox)
     B, P, sp = pts.shape
     V, sv = vox.shape[1], vox.shape[2]
     idx = torch.empty((B, P), dtype=torch.int64, device=pts.device)
-    check(lib.tdssf_devox_nn(_ptr(pts), sp, _ptr(vox), sv, B, P, V, _ptr(idx), _stream(pts)), "tdssf_devox_nn")
+    ws, ws_bytes = None, 0
+    if cell is not None:
+        ws_bytes = lib.tdssf_devox_nn_workspace_bytes(B, P, V)
+        ws = _devox_ws.get(pts.device)
+        if ws is None or ws.numel() < ws_bytes:
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=pts.device)
+            _devox_ws[pts.device] = ws
+    check(lib.tdssf_devox_nn(_ptr(pts), sp, _ptr(vox), sv, B, P, V, _ptr(idx), float(cell or 0.0), _ptr(ws),
+                             ws.numel() if ws is not None else 0, _stream(pts)), "tdssf_devox_nn")
     return idx
 
 

@@ -176,9 +176,16 @@ TDSSF_API int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N,
  * a7  devoxelize: nearest voxel per raw point, gather, and the backward scatter-add
  * replaces  LiDARFeatureEncoder.devoxelize   utils/lidar.py:120-172
  * pts [B,P,pts_stride] / vox [B,V,vox_stride] (xyz first).  idx [B,P] int64 = argmin_v |p-v|^2,
- * first index wins ties.  All V rows take part, zero padding included. */
+ * first index wins ties.  All V rows take part, zero padding included.
+ * workspace == NULL: brute force over all P x V pairs.  With a workspace of tdssf_devox_nn_workspace_bytes(B,P,V)
+ * bytes (256-byte aligned): the voxels are hashed into cubic cells of edge `cell` (same length unit as the
+ * coordinates; any positive value gives the same result, a few voxel sizes is fastest) and each point searches the 27
+ * cells around it; points without a voxel closer than 0.99*cell fall back to the full scan.  Same indices as the brute
+ * force, bit for bit. */
+TDSSF_API size_t tdssf_devox_nn_workspace_bytes(int B, int P, int V);
 TDSSF_API int tdssf_devox_nn(const float* pts, int64_t pts_stride, const float* vox, int64_t vox_stride,
-                   int B, int P, int V, int64_t* idx, void* stream);
+                   int B, int P, int V, int64_t* idx, float cell, void* workspace, size_t workspace_bytes,
+                   void* stream);
 /* out[b,p,:] = scores[b,idx[b,p],:]   scores [B,V,C], out [B,P,C] */
 TDSSF_API int tdssf_devox_gather(const float* scores, const int64_t* idx, int B, int P, int V, int C,
                        float* out, void* stream);

@@ -211,6 +211,45 @@ def test_devoxelize(ops, golden_dir):
     np.testing.assert_allclose(scores.grad.cpu().numpy(), ref, rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize("case", ["voxelised", "sparse", "padded", "degenerate"])
+@pytest.mark.parametrize("cell", [0.1, 0.5, 4.0])
+def test_devox_grid_equals_brute_force(ops, case, cell):
+    """The grid-accelerated nearest-voxel search returns the brute-force indices bit for bit, for any cell size:
+    voxel centres of a real voxelisation, a sparse cloud (most points fall back to the full scan), zero-padded voxel
+    rows, and duplicates / non-finite coordinates / a single voxel."""
+    gen = torch.Generator().manual_seed(11)
+    B, P = 2, 6000
+    pts = synth.make_points(B, P, gen)[..., :3].contiguous()
+    if case == "voxelised":
+        vs = 0.1
+        vox = torch.stack([torch.unique(torch.floor(pts[b] / vs), dim=0)[:4000] * vs + vs / 2 for b in range(B)])
+    elif case == "sparse":
+        vox = synth.make_points(B, 700, gen)[..., :3].contiguous()
+    elif case == "padded":
+        vox = torch.zeros(B, 5000, 3)
+        vox[:, :3000] = pts[:, :3000] + 0.03
+        pts[0, :50] *= 0.01           # points near the origin, where the padding rows sit
+    else:
+        vox = pts[:, :1].clone() if cell == 0.1 else pts[:, :2000].repeat(1, 2, 1)   # one voxel / every voxel twice
+        pts[0, 5] = float("nan")
+        pts[1, 7, 0] = float("inf")
+        vox = vox.clone()
+        if vox.shape[1] > 10:
+            vox[0, 3, 1] = float("nan")
+    pts_d, vox_d = pts.cuda(), vox.cuda()
+    brute = ops.devox_nn(pts_d, vox_d, cell=None)
+    grid = ops.devox_nn(pts_d, vox_d, cell=cell)
+    torch.cuda.synchronize()
+    assert torch.equal(grid, brute)
+    # and the brute force is the exact nearest neighbour wherever it is unambiguous
+    b = 0
+    finite = torch.isfinite(pts[b]).all(-1).numpy()
+    exact = O.devox_nn(pts[b].numpy()[finite], np.nan_to_num(vox[b].numpy(), nan=1e30))
+    best, second = O.devox_gap(pts[b].numpy()[finite], np.nan_to_num(vox[b].numpy(), nan=1e30))
+    clear = (second - best) > 1e-4
+    assert np.array_equal(brute[b].cpu().numpy()[finite][clear], exact[clear])
+
+
 def test_lidar_encoder_contract(ops):
     """forward() pads/caches like utils/lidar.py:27-81 and devoxelize() reads that cache (zero padding searched)."""
     from utils.lidar import LiDARFeatureEncoder

@@ -112,10 +112,25 @@ Bd, P, Vd = 2, 34720, 30000
 gen = torch.Generator().manual_seed(5)
 raw = synth.make_points(Bd, P, gen)[..., :3].contiguous().to(dev)
 vox = (raw[:, torch.randperm(P, generator=gen)[:Vd]] + 0.05).contiguous()
-ms = timeit(lambda: ops.devox_nn(raw, vox), n=5)
-emit("a7", "devox_nn_kernel", ms, Bd * P * Vd, "point-voxel pairs", flops_per_unit=8,
-     note=f"{Bd} sweeps x {P} points x {Vd} voxels, expanded-form distance + running arg-min (~8 flops per pair); "
+ms = timeit(lambda: ops.devox_nn(raw, vox, cell=None), n=5)
+emit("a7", "devox_nn_kernel (brute force)", ms, Bd * P * Vd, "point-voxel pairs", flops_per_unit=8,
+     note=f"{Bd} sweeps x {P} points x {Vd} voxels, direct-difference distance + running arg-min (~8 flops per pair); "
           "the reference materialises a P x V_max matrix")
+ms = timeit(lambda: ops.devox_nn(raw, vox, cell=0.5))
+emit("a7", "devox grid build + query + fallback scan (cell 0.5 m)", ms, Bd * P, "points", bytes_per_unit=16 + 8 + 16 * Vd / P,
+     note="same indices as the brute force; uniformly random synthetic cloud, so the share of fallback points is "
+          "far above a voxelised sweep's")
+# voxel centres of an actual voxelisation of the same points (0.1 m voxels): the reference's situation
+vs = 0.1
+cent = [torch.unique(torch.floor(raw[b] / vs), dim=0) * vs + vs / 2 for b in range(Bd)]
+Vv = min(c.shape[0] for c in cent)
+vox_v = torch.stack([c[:Vv] for c in cent]).contiguous()
+ms = timeit(lambda: ops.devox_nn(raw, vox_v, cell=None), n=5)
+emit("a7", "devox_nn_kernel (brute force), voxelised sweep", ms, Bd * P * Vv, "point-voxel pairs", flops_per_unit=8,
+     note=f"{Vv} occupied 0.1 m voxels per sweep")
+ms = timeit(lambda: ops.devox_nn(raw, vox_v, cell=0.5))
+emit("a7", "devox grid search, voxelised sweep (cell 0.5 m)", ms, Bd * P, "points", bytes_per_unit=16 + 8 + 16 * Vv / P,
+     note="every point lies inside an occupied voxel: no fallback")
 idx = ops.devox_nn(raw, vox)
 scores = torch.randn(Bd, Vd, 16, device=dev)
 ms = timeit(lambda: ops.devox_gather(scores, idx))
