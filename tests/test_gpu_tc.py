@@ -174,3 +174,20 @@ def test_fused_many_sweeps_chunked(ops):
     assert torch.equal(rec, ref_rec)
     ref = ops.mlp_f32(feat, ops.gather_mean(tok, ref_rec), *wd)
     assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
+
+
+@pytest.mark.parametrize("B,V,NC", [(1, 1, 6), (1, 255, 1), (3, 257, 3), (2, 1000, 5), (1, 40000, 6)])
+def test_fused_odd_shapes(ops, B, V, NC):
+    """Tile remainders, a single point, fewer than six cameras: fused kernel against the unfused fp32 route."""
+    sw = synth.make_sweeps(B, V, "dinov2", seed=B * 1000 + V)
+    K, Rt = torch.stack(sw.K)[:, :NC].contiguous(), torch.stack(sw.Rt)[:, :NC].contiguous()
+    tok = sw.tokens[:, :NC].contiguous()
+    w = synth.make_mlp_weights(3)
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    args = (sw.points.cuda(), K.cuda(), Rt.cuda(), sw.image_sizes.float().cuda(), sw.encoder)
+    logits, rec = ops.fusion_fwd(*args, tok.cuda(), sw.point_feat.cuda(), packed, want_rec=True)
+    ref_rec = ops.project(*args, want_pix=False, want_depth=False, want_valid=False, want_rec=True)["rec"]
+    assert torch.equal(rec, ref_rec)
+    ref = ops.mlp_f32(sw.point_feat.cuda(), ops.gather_mean(tok.cuda(), ref_rec), *wd)
+    assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
