@@ -104,6 +104,7 @@ struct Params {
   int B, V, NC, resize_h, resize_w, patch, M;
   const void* tokens;
   tdssf_rec* rec_out;          // optional
+  int64_t* preds_out;          // optional: argmax over the 16 logits + 1 (the class ids of utils/losses.py:66 / utils/test.py)
   const float* x_img;          // dense mode
   const float* x_pt;           // [N,64]
   const uint8_t* packed;       // weights image (tdssf_mlp_pack_weights)
@@ -716,12 +717,23 @@ fused_mlp_kernel(const Params p) {
         if (warp == 0) TRACE(p.debug, 9, it);
         if (row < p.N) {
           float4* dst = reinterpret_cast<float4*>(p.logits + row * kClasses);
+          float best = -INFINITY;
+          int arg = 0;
+          bool nan_seen = false;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float4 bq = *reinterpret_cast<const float4*>(s_bias + kN1 + kN2 + 4 * j);
-            dst[j] = make_float4(__uint_as_float(v[4 * j]) + bq.x, __uint_as_float(v[4 * j + 1]) + bq.y,
-                                 __uint_as_float(v[4 * j + 2]) + bq.z, __uint_as_float(v[4 * j + 3]) + bq.w);
+            const float4 o = make_float4(__uint_as_float(v[4 * j]) + bq.x, __uint_as_float(v[4 * j + 1]) + bq.y,
+                                         __uint_as_float(v[4 * j + 2]) + bq.z, __uint_as_float(v[4 * j + 3]) + bq.w);
+            dst[j] = o;
+            const float e[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {  // torch.argmax: first maximum, a NaN counts as the maximum
+              const bool is_nan = e[k] != e[k];
+              if (!nan_seen && (is_nan || e[k] > best || (j == 0 && k == 0))) { best = e[k]; arg = 4 * j + k; nan_seen = is_nan; }
+            }
           }
+          if (p.preds_out) p.preds_out[row] = arg + 1;
         }
       }
     }
@@ -1166,6 +1178,7 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
                                 const float* Rt, const float* img_hw, int B, int V, int NC, int resize_h,
                                 int resize_w, int patch, const void* tokens, int tok_dtype, int M, int Ci,
                                 const float* x_pt, const void* packed_weights, float* logits, tdssf_rec* rec_out,
+                                int64_t* preds_out,
                                 void* workspace, size_t workspace_bytes, void* stream) {
   using namespace tdssf;
   TDSSF_REQUIRE(xyz && K && Rt && img_hw && tokens && x_pt && packed_weights && logits, "tdssf_fusion_fwd: NULL pointer");
@@ -1208,7 +1221,7 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
     p.K = K + (int64_t)b0 * NC * 9; p.Rt = Rt + (int64_t)b0 * NC * 16; p.img_hw = img_hw + 2 * (int64_t)b0;
     p.B = Bc; p.V = V; p.NC = NC; p.resize_h = resize_h; p.resize_w = resize_w; p.patch = patch; p.M = M;
     p.tokens = reinterpret_cast<const char*>(tokens) + (size_t)b0 * NC * M * tok_row;
-    p.rec_out = rec_out ? rec_out + row0 : nullptr; p.x_img = nullptr; p.x_pt = x_pt + row0 * tc::kCp;
+    p.rec_out = rec_out ? rec_out + row0 : nullptr; p.preds_out = preds_out ? preds_out + row0 : nullptr; p.x_img = nullptr; p.x_pt = x_pt + row0 * tc::kCp;
     p.packed = (const uint8_t*)packed_weights; p.logits = logits + row0 * tc::kClasses; p.N = Nc;
     p.n_pairs = (int)ceil_div(Nc, 2 * tc::kTileM);
     p.debug = tc::debug_word();

@@ -225,8 +225,9 @@ def _fusion_workspace(device, B, V, tok_code):
     return ws
 
 
-def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None):
-    """Fully fused inference: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) -> logits (B,V,16)."""
+def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None, preds_out=None):
+    """Fully fused inference: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) -> logits (B,V,16).
+    preds_out: optional CUDA int64 (B,V) that receives argmax(logits)+1 (class ids 1..16) from the same launch."""
     _need_cuda(points, K, Rt, img_hw, tokens, x_pt, packed)
     pts, ss, ps = _points_layout(points)
     B, V, _ = pts.shape
@@ -237,11 +238,14 @@ def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=Fa
     xp = _f32c(x_pt)
     logits = out if out is not None else torch.empty((B, V, 16), dtype=torch.float32, device=pts.device)
     rec = torch.empty((B, V, 4), dtype=torch.int32, device=pts.device) if want_rec else None
+    if preds_out is not None and (preds_out.dtype != torch.int64 or not preds_out.is_cuda or preds_out.numel() != B * V
+                                  or not preds_out.is_contiguous()):
+        raise ValueError("preds_out must be a contiguous CUDA int64 tensor with B*V elements")
     ws = _fusion_workspace(pts.device, B, V, _TOK_DTYPES[tokens.dtype])
     check(lib.tdssf_fusion_fwd(_ptr(pts), ss, ps, _ptr(_f32c(K)), _ptr(_f32c(Rt)), _ptr(_f32c(img_hw)), B, V, NC,
                                int(encoder.resize_height), int(encoder.resize_width), int(encoder.patch_size),
                                _ptr(tokens), _TOK_DTYPES[tokens.dtype], M, Ci, _ptr(xp), _ptr(packed), _ptr(logits),
-                               _ptr(rec), _ptr(ws), ws.numel(), _stream(pts)), "tdssf_fusion_fwd")
+                               _ptr(rec), _ptr(preds_out), _ptr(ws), ws.numel(), _stream(pts)), "tdssf_fusion_fwd")
     return (logits, rec) if want_rec else logits
 
 

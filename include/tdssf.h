@@ -154,6 +154,8 @@ TDSSF_API int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w_host, void* pack
  * x_pt    [B*V,64] fp32 point features (PTv3 output)
  * logits  [B*V,16] fp32
  * rec_out optional [B,V] camera-assignment records (NULL to skip).
+ * preds_out optional [B*V] int64 class ids = argmax(logits) + 1 (first maximum, like torch.argmax; utils/losses.py:66),
+ *          for the evaluation loop's confusion matrix (NULL to skip).
  * workspace: tdssf_fusion_workspace_bytes(B, V, tok_dtype) bytes, 256-byte aligned.  Holds, per point, the address of
  *          the token row the gather will read, and for the points seen by several cameras their camera mean (worst case
  *          one token row per point; only the rows of such points are ever touched).  Scratch: nothing persists between
@@ -164,7 +166,7 @@ TDSSF_API int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t p
                      int B, int V, int NC, int resize_h, int resize_w, int patch,
                      const void* tokens, int tok_dtype, int M, int Ci,
                      const float* x_pt, const void* packed_weights,
-                     float* logits, tdssf_rec* rec_out,
+                     float* logits, tdssf_rec* rec_out, int64_t* preds_out,
                      void* workspace, size_t workspace_bytes, void* stream);
 
 /* tensor-core MLP on pre-gathered features (used by training forward and as the unfused check).

@@ -191,3 +191,19 @@ def test_fused_odd_shapes(ops, B, V, NC):
     assert torch.equal(rec, ref_rec)
     ref = ops.mlp_f32(sw.point_feat.cuda(), ops.gather_mean(tok.cuda(), ref_rec), *wd)
     assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
+
+
+def test_fused_preds_out(ops):
+    """The class ids written by the fused launch are torch.argmax(logits) + 1 of the logits it wrote (utils/losses.py:66)."""
+    sw = synth.make_sweeps(2, 5000, "dinov3", seed=21)
+    w = synth.make_mlp_weights(21)
+    packed = ops.pack_weights(*[w[k].cuda() for k in W_KEYS])
+    preds = torch.zeros(2, 5000, dtype=torch.int64, device="cuda")
+    logits = ops.fusion_fwd(sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(),
+                            sw.image_sizes.float().cuda(), sw.encoder, sw.tokens.cuda(), sw.point_feat.cuda(), packed,
+                            preds_out=preds)
+    assert torch.equal(preds, logits.argmax(-1) + 1)
+    assert int(preds.min()) >= 1 and int(preds.max()) <= 16
+    with pytest.raises(ValueError):
+        ops.fusion_fwd(sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda(),
+                       sw.encoder, sw.tokens.cuda(), sw.point_feat.cuda(), packed, preds_out=preds.int())
