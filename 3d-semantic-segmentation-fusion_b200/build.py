@@ -78,7 +78,7 @@ def build(force=False, verbose=False, defines=(), out=None):
         raise RuntimeError("nvcc failed; see messages above")
     objs = [os.path.join(OBJ, f[:-3] + ".o") for f in sources]
     if force or jobs or not os.path.exists(LIB):
-        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs, "-lcudart"]
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs, "-lcudart", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stdout + r.stderr)

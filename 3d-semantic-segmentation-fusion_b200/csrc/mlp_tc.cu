@@ -104,6 +104,8 @@ struct Params {
   int B, V, NC, resize_h, resize_w, patch, M;
   const void* tokens;
   tdssf_rec* rec_out;          // optional
+  uint16_t* h1_out;            // optional [N,256] bf16: post-ReLU activations of layer 1, saved for the backward pass
+  uint16_t* h2_out;            // optional [N,64] bf16
   int64_t* preds_out;          // optional: argmax over the 16 logits + 1 (the class ids of utils/losses.py:66 / utils/test.py)
   const float* x_img;          // dense mode
   const float* x_pt;           // [N,64]
@@ -649,6 +651,7 @@ fused_mlp_kernel(const Params p) {
       const uint32_t buf = it & 1, par = (it >> 1) & 1;
       const int64_t row = tile_row0(it) + row_in_tile;
       const uint32_t tb = tlane + buf * 256;
+      const bool save_h1 = p.h1_out != nullptr && row < p.N, save_h2 = p.h2_out != nullptr && row < p.N;
       // ---- layer 1: acc1 cols [128ch, 128ch+128) -> relu(+b1) -> bf16 H1 cols [128ch, 128ch+64), in place --------
       wait_bar(bar(kBarAcc1Full + buf), par, p.debug, 7);
       ptx::tc_fence_after();
@@ -665,10 +668,20 @@ fused_mlp_kernel(const Params p) {
           ptx::tmem_ld16(src + (c + 1) * 16, vb);
           act16(va, bias + c * 16, h);
           ptx::tmem_st8(src + c * 8, h);
+          if (save_h1) {
+            uint4* d = reinterpret_cast<uint4*>(p.h1_out + row * kN1 + ch * 128 + c * 16);
+            d[0] = make_uint4(h[0], h[1], h[2], h[3]);
+            d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+          }
           ptx::tmem_wait_ld();
           if (c + 2 < 8) ptx::tmem_ld16(src + (c + 2) * 16, va);
           act16(vb, bias + (c + 1) * 16, h);
           ptx::tmem_st8(src + (c + 1) * 8, h);
+          if (save_h1) {
+            uint4* d = reinterpret_cast<uint4*>(p.h1_out + row * kN1 + ch * 128 + (c + 1) * 16);
+            d[0] = make_uint4(h[0], h[1], h[2], h[3]);
+            d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+          }
         }
       }
 #endif
@@ -692,8 +705,18 @@ fused_mlp_kernel(const Params p) {
         ptx::tmem_wait_ld();
         act16(va, bias, h);
         ptx::tmem_st8(dst, h);
+        if (save_h2) {
+          uint4* d = reinterpret_cast<uint4*>(p.h2_out + row * kN2 + ch * 32);
+          d[0] = make_uint4(h[0], h[1], h[2], h[3]);
+          d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+        }
         act16(vb, bias + 16, h);
         ptx::tmem_st8(dst + 8, h);
+        if (save_h2) {
+          uint4* d = reinterpret_cast<uint4*>(p.h2_out + row * kN2 + ch * 32 + 16);
+          d[0] = make_uint4(h[0], h[1], h[2], h[3]);
+          d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+        }
       }
 #endif
       ptx::tmem_wait_st();
@@ -1238,16 +1261,18 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
 }
 
 extern "C" int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N, const void* packed_weights,
-                                float* logits, void* stream) {
+                                float* logits, void* h1_bf16, void* h2_bf16, void* stream) {
   using namespace tdssf;
   TDSSF_REQUIRE(x_pt && x_img && packed_weights && logits, "tdssf_mlp_fwd_tc: NULL pointer");
   TDSSF_REQUIRE(N >= 0, "tdssf_mlp_fwd_tc: negative N");
-  TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)logits | (uintptr_t)packed_weights) & 15) == 0,
+  TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)logits | (uintptr_t)packed_weights | (uintptr_t)h1_bf16 |
+                  (uintptr_t)h2_bf16) & 15) == 0,
                 "tdssf_mlp_fwd_tc: pointers must be 16-byte aligned");
   if (N == 0) return TDSSF_OK;
   if (int rc = tdssf_check_device()) return rc;
   tc::Params p = {};
   p.x_img = x_img; p.x_pt = x_pt; p.packed = (const uint8_t*)packed_weights; p.logits = logits; p.N = N;
+  p.h1_out = reinterpret_cast<uint16_t*>(h1_bf16); p.h2_out = reinterpret_cast<uint16_t*>(h2_bf16);
   p.B = 1; p.V = 1; p.NC = 1; p.M = 1;
   p.n_pairs = (int)ceil_div(N, 2 * tc::kTileM);
   p.debug = tc::debug_word();

@@ -209,8 +209,55 @@ def mlp_tc(x_pt, x_img, packed) -> torch.Tensor:
     xi = _f32c(x_img).reshape(-1, 384)
     N = xp.shape[0]
     logits = torch.empty((N, 16), dtype=torch.float32, device=xp.device)
-    check(lib.tdssf_mlp_fwd_tc(_ptr(xp), _ptr(xi), N, _ptr(packed), _ptr(logits), _stream(xp)), "tdssf_mlp_fwd_tc")
+    check(lib.tdssf_mlp_fwd_tc(_ptr(xp), _ptr(xi), N, _ptr(packed), _ptr(logits), None, None, _stream(xp)),
+          "tdssf_mlp_fwd_tc")
     return logits.reshape(*shape, 16)
+
+
+class _MlpTC(torch.autograd.Function):
+    """Training through the tensor cores: tcgen05 forward that saves its bf16 activations, bf16 backward
+    (tdssf_mlp_bwd_tc).  Tolerance 1e-2 (north_star's bf16 bound); `mlp_f32` is the 1e-5 parity mode."""
+
+    @staticmethod
+    def forward(ctx, x_pt, x_img, W1, b1, W2, b2, W3, b3):
+        _need_cuda(x_pt, x_img, W1)
+        shape = x_pt.shape[:-1]
+        xp = _f32c(x_pt).reshape(-1, 64)
+        xi = _f32c(x_img).reshape(-1, 384)
+        params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
+        _weights_struct(params)  # shape check
+        N = xp.shape[0]
+        dev = xp.device
+        packed = pack_weights(*params)
+        h1 = torch.empty((N, 256), dtype=torch.bfloat16, device=dev)
+        h2 = torch.empty((N, 64), dtype=torch.bfloat16, device=dev)
+        logits = torch.empty((N, 16), dtype=torch.float32, device=dev)
+        check(lib.tdssf_mlp_fwd_tc(_ptr(xp), _ptr(xi), N, _ptr(packed), _ptr(logits), _ptr(h1), _ptr(h2), _stream(xp)),
+              "tdssf_mlp_fwd_tc")
+        ctx.save_for_backward(xp, xi, h1, h2, *params)
+        ctx.in_shape = tuple(x_pt.shape)
+        return logits.reshape(*shape, 16)
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        xp, xi, h1, h2, W1, b1, W2, b2, W3, b3 = ctx.saved_tensors
+        N = xp.shape[0]
+        dev = xp.device
+        dl = _f32c(dlogits).reshape(-1, 16)
+        grads = [torch.zeros_like(t) for t in (W1, b1, W2, b2, W3, b3)]
+        dx_pt = torch.empty((N, 64), dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
+        ws_bytes = lib.tdssf_mlp_bwd_tc_workspace_bytes(N)
+        work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        w = _weights_struct([W1, b1, W2, b2, W3, b3])
+        g = _lib.MlpGrads(*[t.data_ptr() for t in grads])
+        check(lib.tdssf_mlp_bwd_tc(_ptr(xp), _ptr(xi), _ptr(h1), _ptr(h2), _ptr(dl), N, C.byref(w), C.byref(g),
+                                   _ptr(dx_pt), _ptr(work), ws_bytes, _stream(xp)), "tdssf_mlp_bwd_tc")
+        return (dx_pt.reshape(ctx.in_shape) if dx_pt is not None else None, None, *grads)
+
+
+def mlp_tc_train(x_pt, x_img, W1, b1, W2, b2, W3, b3):
+    """bf16 tensor-core MLP, differentiable w.r.t. x_pt and the six parameters (1e-2 tolerance)."""
+    return _MlpTC.apply(x_pt, x_img, W1, b1, W2, b2, W3, b3)
 
 
 _fusion_ws = {}  # device index -> workspace tensor (scratch; grown on demand, reused by every call on that device)

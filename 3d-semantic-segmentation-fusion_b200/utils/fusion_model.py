@@ -9,8 +9,8 @@ Reference interface mirrored (file:line in the reference tree):
                  cam_intrinsics, lidar2cam_extrinsics) -> point_scores                        :152-207
 
 MLP arithmetic is selected with the environment variable TDSSF_MLP:
-    bf16 (default)  inference through the fully fused tcgen05 kernel (1e-2 tolerance, north_star);
-                    whenever a gradient is required the fp32 kernels are used
+    bf16 (default)  inference through the fully fused tcgen05 kernel; when a gradient is required: projection + gather
+                    kernels, tcgen05 forward that saves its bf16 activations, bf16 backward (1e-2 tolerance, north_star)
     fp32            fp32 CUDA-core kernels everywhere (1e-5 tolerance)
 """
 from __future__ import annotations
@@ -127,7 +127,10 @@ class FeatureFusionModel(nn.Module):
             rec = ops.project(voxel_raw, K, Rt, hw, enc, want_pix=False, want_depth=False, want_valid=False,
                               want_rec=True)["rec"]
             fused_img_feat = ops.gather_mean(tokens, rec)
-            voxel_scores = ops.mlp_f32(voxel_features, fused_img_feat, *params)
+            if mode == "bf16" and dim == 384 and self.mlp[0].in_features == 448:
+                voxel_scores = ops.mlp_tc_train(voxel_features, fused_img_feat, *params)   # training, tensor cores
+            else:
+                voxel_scores = ops.mlp_f32(voxel_features, fused_img_feat, *params)
 
         point_scores, _ = self.pcd_encoder.devoxelize(voxel_scores)
         return point_scores

@@ -169,10 +169,23 @@ TDSSF_API int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t p
                      float* logits, tdssf_rec* rec_out, int64_t* preds_out,
                      void* workspace, size_t workspace_bytes, void* stream);
 
-/* tensor-core MLP on pre-gathered features (used by training forward and as the unfused check).
- * x_img may be fp32 [N,384].  h1_bf16 / h2_bf16 optional saved activations. */
+/* tensor-core MLP on pre-gathered features (training forward, and the unfused check of the fused kernel).
+ * x_img fp32 [N,384].  h1_bf16 [N,256] / h2_bf16 [N,64]: optional (NULL to skip) post-ReLU activations in bf16, exactly
+ * the values the next layer consumed, saved for tdssf_mlp_bwd_tc. */
 TDSSF_API int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N, const void* packed_weights,
-                     float* logits, void* stream);
+                     float* logits, void* h1_bf16, void* h2_bf16, void* stream);
+
+/* bf16 backward of the MLP from the activations tdssf_mlp_fwd_tc saved (training with the tensor-core forward).
+ * replaces  the autograd of FeatureFusionModel.mlp   utils/fusion_model.py:144-150,203-204 (utils/train.py:91)
+ * Accumulates (+=) dW*, db* into the caller's fp32 buffers (zeroed by the caller) and writes dx_pt [N,64] (may be NULL).
+ * The six products are plain GEMMs and run in cuBLAS (bf16 operands, fp32 accumulate), loaded at first use; the
+ * conversions, ReLU masks and bias-gradient sums are kernels of this library.  TDSSF_ENOSUP if cuBLAS cannot be loaded.
+ * workspace: tdssf_mlp_bwd_tc_workspace_bytes(N), 256-byte aligned. */
+TDSSF_API size_t tdssf_mlp_bwd_tc_workspace_bytes(int64_t N);
+TDSSF_API int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* h1_bf16, const void* h2_bf16,
+                     const float* dlogits, int64_t N, const tdssf_mlp_weights* w_host,
+                     const tdssf_mlp_grads* g_host, float* dx_pt,
+                     void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a7  devoxelize: nearest voxel per raw point, gather, and the backward scatter-add
