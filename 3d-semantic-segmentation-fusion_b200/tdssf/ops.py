@@ -260,15 +260,16 @@ def mlp_tc_train(x_pt, x_img, W1, b1, W2, b2, W3, b3):
     return _MlpTC.apply(x_pt, x_img, W1, b1, W2, b2, W3, b3)
 
 
-_fusion_ws = {}  # device index -> workspace tensor (scratch; grown on demand, reused by every call on that device)
+_fusion_ws = {}  # (device index, stream) -> workspace tensor: scratch of the launches queued on that stream, grown on demand
 
 
 def _fusion_workspace(device, B, V, tok_code):
     need = lib.tdssf_fusion_workspace_bytes(B, V, tok_code)
-    ws = _fusion_ws.get(device.index)
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _fusion_ws.get(key)
     if ws is None or ws.numel() < need:
         ws = torch.empty(need, dtype=torch.uint8, device=device)
-        _fusion_ws[device.index] = ws
+        _fusion_ws[key] = ws
     return ws
 
 
@@ -315,10 +316,11 @@ def devox_nn(pts: torch.Tensor, vox: torch.Tensor, cell: Optional[float] = 0.25)
     ws, ws_bytes = None, 0
     if cell is not None:
         ws_bytes = lib.tdssf_devox_nn_workspace_bytes(B, P, V)
-        ws = _devox_ws.get(pts.device)
+        key = (pts.device.index, torch.cuda.current_stream(pts.device).cuda_stream)
+        ws = _devox_ws.get(key)
         if ws is None or ws.numel() < ws_bytes:
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=pts.device)
-            _devox_ws[pts.device] = ws
+            _devox_ws[key] = ws
     check(lib.tdssf_devox_nn(_ptr(pts), sp, _ptr(vox), sv, B, P, V, _ptr(idx), float(cell or 0.0), _ptr(ws),
                              ws.numel() if ws is not None else 0, _stream(pts)), "tdssf_devox_nn")
     return idx
