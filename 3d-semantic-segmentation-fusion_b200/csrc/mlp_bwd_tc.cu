@@ -137,13 +137,20 @@ mask_cvt_colsum_kernel(const float* __restrict__ G, const uint16_t* __restrict__
       *reinterpret_cast<uint4*>(out + r * C + c) = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
     }
   }
+  // lanes l and l + kTx, l + 2 kTx, ... of a warp hold the same columns: butterfly over them, then one shared-memory
+  // atomic per warp and column, one global atomic per block and column
   __shared__ float s_sum[C];
   for (int c = threadIdx.x; c < C; c += 256) s_sum[c] = 0.f;
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < kJ; ++j)
 #pragma unroll
-    for (int e = 0; e < 8; ++e) atomicAdd(&s_sum[(tx + j * kTx) * 8 + e], acc[j][e]);
+    for (int e = 0; e < 8; ++e) {
+      float v = acc[j][e];
+#pragma unroll
+      for (int o = 16; o >= kTx; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if ((threadIdx.x & 31) < kTx) atomicAdd(&s_sum[(tx + j * kTx) * 8 + e], v);
+    }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += 256) atomicAdd(db + c, s_sum[c]);
 }
