@@ -183,19 +183,19 @@ extern "C" size_t tdssf_mlp_bwd_tc_workspace_bytes(int64_t N) {
   return tdssf::bwd::carve(N < 0 ? 0 : N, nullptr, nullptr) + 256;
 }
 
-extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* h1_bf16, const void* h2_bf16,
+extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* x_bf16, const void* h1_bf16, const void* h2_bf16,
                                 const float* dlogits, int64_t N, const tdssf_mlp_weights* w_host,
                                 const tdssf_mlp_grads* g_host, float* dx_pt, void* workspace, size_t workspace_bytes,
                                 void* stream) {
   using namespace tdssf;
   using namespace tdssf::bwd;
-  TDSSF_REQUIRE(x_pt && x_img && h1_bf16 && h2_bf16 && dlogits && w_host && g_host, "tdssf_mlp_bwd_tc: NULL pointer");
+  TDSSF_REQUIRE((x_bf16 || (x_pt && x_img)) && h1_bf16 && h2_bf16 && dlogits && w_host && g_host, "tdssf_mlp_bwd_tc: NULL pointer");
   TDSSF_REQUIRE(w_host->W1 && w_host->W2 && w_host->W3, "tdssf_mlp_bwd_tc: NULL weight pointer");
   TDSSF_REQUIRE(g_host->dW1 && g_host->db1 && g_host->dW2 && g_host->db2 && g_host->dW3 && g_host->db3,
                 "tdssf_mlp_bwd_tc: NULL gradient pointer");
   TDSSF_REQUIRE(N >= 0 && N < (1ll << 31), "tdssf_mlp_bwd_tc: N out of range");
   if (N == 0) return TDSSF_OK;
-  TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)h1_bf16 | (uintptr_t)h2_bf16 | (uintptr_t)dlogits |
+  TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)x_bf16 | (uintptr_t)h1_bf16 | (uintptr_t)h2_bf16 | (uintptr_t)dlogits |
                   (uintptr_t)dx_pt) & 15) == 0, "tdssf_mlp_bwd_tc: pointers must be 16-byte aligned");
   TDSSF_REQUIRE(workspace && ((uintptr_t)workspace & 255) == 0 && workspace_bytes >= tdssf_mlp_bwd_tc_workspace_bytes(N),
                 "tdssf_mlp_bwd_tc: 256-byte aligned workspace of %zu bytes needed, got %zu",
@@ -218,7 +218,11 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
   cvt_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W1, reinterpret_cast<uint4*>(w.W1), (int64_t)kN1 * kK1 / 8);
   cvt_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W2, reinterpret_cast<uint4*>(w.W2), (int64_t)kN2 * kN1 / 8);
   cvt_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W3, reinterpret_cast<uint4*>(w.W3), (int64_t)kC * kN2 / 8);
-  concat_bf16_kernel<<<blocks, 256, 0, s>>>(x_pt, x_img, reinterpret_cast<uint4*>(w.X), N);
+  const void* X = x_bf16;
+  if (!X) {
+    concat_bf16_kernel<<<blocks, 256, 0, s>>>(x_pt, x_img, reinterpret_cast<uint4*>(w.X), N);
+    X = w.X;
+  }
   mask_cvt_colsum_kernel<kC><<<blocks, 256, 0, s>>>(dlogits, nullptr, w.dl, g_host->db3, N);
   TDSSF_LAUNCH_CHECK();
   const int n = (int)N;
@@ -237,6 +241,6 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
   // weight gradients, accumulated into the caller's fp32 buffers
   if (!ok(gemm_rm(h, true, false, kC, kN2, n, 1.f, w.dl, kC, h2_bf16, kN2, 1.f, g_host->dW3, kN2), "dW3")) return TDSSF_ECUDA;
   if (!ok(gemm_rm(h, true, false, kN2, kN1, n, 1.f, w.dh2, kN2, h1_bf16, kN1, 1.f, g_host->dW2, kN1), "dW2")) return TDSSF_ECUDA;
-  if (!ok(gemm_rm(h, true, false, kN1, kK1, n, 1.f, w.dh1, kN1, w.X, kK1, 1.f, g_host->dW1, kK1), "dW1")) return TDSSF_ECUDA;
+  if (!ok(gemm_rm(h, true, false, kN1, kK1, n, 1.f, w.dh1, kN1, X, kK1, 1.f, g_host->dW1, kK1), "dW1")) return TDSSF_ECUDA;
   return TDSSF_OK;
 }

@@ -104,6 +104,7 @@ struct Params {
   int B, V, NC, resize_h, resize_w, patch, M;
   const void* tokens;
   tdssf_rec* rec_out;          // optional
+  uint16_t* x_out;             // optional [N,448] bf16: the MLP input [point feature | image feature] as the tensor cores saw it
   uint16_t* h1_out;            // optional [N,256] bf16: post-ReLU activations of layer 1, saved for the backward pass
   uint16_t* h2_out;            // optional [N,64] bf16
   int64_t* preds_out;          // optional: argmax over the 16 logits + 1 (the class ids of utils/losses.py:66 / utils/test.py)
@@ -550,7 +551,8 @@ __device__ __forceinline__ void project_rows(const Params& p, uint32_t cal_addr,
 }
 
 // kGather: image channels come from the token maps through the records; else from p.x_img
-template <typename TokT, bool kGather>
+// kSave: training launch, the bf16 input rows / hidden activations also go to p.x_out / p.h1_out / p.h2_out
+template <typename TokT, bool kGather, bool kSave>
 __global__ void __launch_bounds__(kThreads, 1)
 fused_mlp_kernel(const Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -651,7 +653,7 @@ fused_mlp_kernel(const Params p) {
       const uint32_t buf = it & 1, par = (it >> 1) & 1;
       const int64_t row = tile_row0(it) + row_in_tile;
       const uint32_t tb = tlane + buf * 256;
-      const bool save_h1 = p.h1_out != nullptr && row < p.N, save_h2 = p.h2_out != nullptr && row < p.N;
+      const bool save_h1 = kSave && p.h1_out != nullptr && row < p.N, save_h2 = kSave && p.h2_out != nullptr && row < p.N;
       // ---- layer 1: acc1 cols [128ch, 128ch+128) -> relu(+b1) -> bf16 H1 cols [128ch, 128ch+64), in place --------
       wait_bar(bar(kBarAcc1Full + buf), par, p.debug, 7);
       ptx::tc_fence_after();
@@ -933,7 +935,7 @@ fused_mlp_kernel(const Params p) {
 
     uint32_t stage = 0, phase = 0;  // A ring cursor
     // conversion + store of one step of slab S out of set c into ring slot `stage`
-    auto consume_one = [&](auto S_, int st, const Set& c, uint32_t slab_off) {
+    auto consume_one = [&](auto S_, int it, int st, const Set& c, uint32_t slab_off) {
       constexpr int S = decltype(S_)::value;
       constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
 #if defined(TDSSF_EXP_NOPROD) || defined(TDSSF_EXP_NOSTORE)  // (timing experiments: no conversion, no stores)
@@ -941,14 +943,25 @@ fused_mlp_kernel(const Params p) {
       return;
 #endif
       float acc[8];
+      // training: the bf16 input row also goes to HBM for the weight gradient (x_out), 64 contiguous bytes per quarter-warp
+      const int64_t row = tile_row0(it) + pw * kRowsPerWarp + row_of(st, quarter);
+      uint16_t* xo = (kSave && p.x_out && row < p.N) ? p.x_out + row * kK1 + S * kSlabK : nullptr;
       if (kF32) {
         raw8_f32_to_f8(c.a[st], acc);
-        ptx::sts64(so_lo[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]));
-        ptx::sts64(so_hi[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+        const uint32_t w0 = pack_bf16(acc[0], acc[1]), w1 = pack_bf16(acc[2], acc[3]), w2 = pack_bf16(acc[4], acc[5]),
+                       w3 = pack_bf16(acc[6], acc[7]);
+        ptx::sts64(so_lo[st & 1] + slab_off + (st >> 1) * 1024, w0, w1);
+        ptx::sts64(so_hi[st & 1] + slab_off + (st >> 1) * 1024, w2, w3);
+        if (xo) {
+          *reinterpret_cast<uint2*>(xo + 4 * ql) = make_uint2(w0, w1);
+          *reinterpret_cast<uint2*>(xo + 32 + 4 * ql) = make_uint2(w2, w3);
+        }
       } else {
         TokRaw<TokT>::to_f8(c.a[st], acc);
-        ptx::sts128(so_16[st & 1] + slab_off + (st >> 1) * 1024, pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
-                    pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+        const uint32_t w0 = pack_bf16(acc[0], acc[1]), w1 = pack_bf16(acc[2], acc[3]), w2 = pack_bf16(acc[4], acc[5]),
+                       w3 = pack_bf16(acc[6], acc[7]);
+        ptx::sts128(so_16[st & 1] + slab_off + (st >> 1) * 1024, w0, w1, w2, w3);
+        if (xo) *reinterpret_cast<uint4*>(xo + 8 * ql) = make_uint4(w0, w1, w2, w3);
       }
     };
     // One pipeline step: the loads of slab S2 of tile it2 go into set `nxt` (all eight of the thread at once, before
@@ -970,7 +983,7 @@ fused_mlp_kernel(const Params p) {
       if (pw == 0 && it >= 4 && it < 8) TRACE(p.debug, 14, (it - 4) * 7 + S);   // ring slot free
       const uint32_t slab_off = stage * kASlab;
 #pragma unroll
-      for (int st = 0; st < kSteps; ++st) consume_one(S_, st, cur, slab_off);
+      for (int st = 0; st < kSteps; ++st) consume_one(S_, it, st, cur, slab_off);
       ptx::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
@@ -1076,9 +1089,9 @@ __global__ void pack_weights_kernel(const float* __restrict__ W1, const float* _
   }
 }
 
-template <typename TokT, bool kGather>
-static int launch(const Params& p, cudaStream_t s) {
-  auto kern = fused_mlp_kernel<TokT, kGather>;
+template <typename TokT, bool kGather, bool kSave>
+static int launch_as(const Params& p, cudaStream_t s) {
+  auto kern = fused_mlp_kernel<TokT, kGather, kSave>;
   const int smem = kSmemBytes + 1024;
   static bool configured = false;  // per instantiation
   if (!configured) {
@@ -1150,6 +1163,12 @@ static int launch(const Params& p, cudaStream_t s) {
   return TDSSF_OK;
 }
 
+// the training instantiation only when something is to be saved: the inference kernel carries none of that code
+template <typename TokT, bool kGather>
+static int launch(const Params& p, cudaStream_t s) {
+  return (p.x_out || p.h1_out || p.h2_out) ? launch_as<TokT, kGather, true>(p, s) : launch_as<TokT, kGather, false>(p, s);
+}
+
 __device__ __align__(16) unsigned char g_zero_rows[4096];  // zero-initialised at module load, never written
 
 static const void* zero_rows() {
@@ -1201,7 +1220,7 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
                                 const float* Rt, const float* img_hw, int B, int V, int NC, int resize_h,
                                 int resize_w, int patch, const void* tokens, int tok_dtype, int M, int Ci,
                                 const float* x_pt, const void* packed_weights, float* logits, tdssf_rec* rec_out,
-                                int64_t* preds_out,
+                                int64_t* preds_out, void* x_bf16, void* h1_bf16, void* h2_bf16,
                                 void* workspace, size_t workspace_bytes, void* stream) {
   using namespace tdssf;
   TDSSF_REQUIRE(xyz && K && Rt && img_hw && tokens && x_pt && packed_weights && logits, "tdssf_fusion_fwd: NULL pointer");
@@ -1217,7 +1236,8 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
     return TDSSF_ENOSUP;
   }
   TDSSF_REQUIRE((((uintptr_t)tokens | (uintptr_t)x_pt | (uintptr_t)logits | (uintptr_t)packed_weights) & 15) == 0 &&
-                    (!rec_out || ((uintptr_t)rec_out & 15) == 0),
+                    (!rec_out || ((uintptr_t)rec_out & 15) == 0) &&
+                    (((uintptr_t)x_bf16 | (uintptr_t)h1_bf16 | (uintptr_t)h2_bf16) & 15) == 0,
                 "tdssf_fusion_fwd: pointers must be 16-byte aligned");
   const int64_t N = (int64_t)B * V;
   if (N == 0) return TDSSF_OK;
@@ -1244,7 +1264,10 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
     p.K = K + (int64_t)b0 * NC * 9; p.Rt = Rt + (int64_t)b0 * NC * 16; p.img_hw = img_hw + 2 * (int64_t)b0;
     p.B = Bc; p.V = V; p.NC = NC; p.resize_h = resize_h; p.resize_w = resize_w; p.patch = patch; p.M = M;
     p.tokens = reinterpret_cast<const char*>(tokens) + (size_t)b0 * NC * M * tok_row;
-    p.rec_out = rec_out ? rec_out + row0 : nullptr; p.preds_out = preds_out ? preds_out + row0 : nullptr; p.x_img = nullptr; p.x_pt = x_pt + row0 * tc::kCp;
+    p.rec_out = rec_out ? rec_out + row0 : nullptr; p.preds_out = preds_out ? preds_out + row0 : nullptr; p.x_img = nullptr;
+    p.x_out = x_bf16 ? reinterpret_cast<uint16_t*>(x_bf16) + row0 * tc::kK1 : nullptr;
+    p.h1_out = h1_bf16 ? reinterpret_cast<uint16_t*>(h1_bf16) + row0 * tc::kN1 : nullptr;
+    p.h2_out = h2_bf16 ? reinterpret_cast<uint16_t*>(h2_bf16) + row0 * tc::kN2 : nullptr; p.x_pt = x_pt + row0 * tc::kCp;
     p.packed = (const uint8_t*)packed_weights; p.logits = logits + row0 * tc::kClasses; p.N = Nc;
     p.n_pairs = (int)ceil_div(Nc, 2 * tc::kTileM);
     p.debug = tc::debug_word();

@@ -45,10 +45,10 @@ SIGNATURES = {
     "tdssf_mlp_pack_bytes": (_sz, []),
     "tdssf_mlp_pack_weights": (_i, [C.POINTER(MlpWeights), _p, _p]),
     "tdssf_fusion_workspace_bytes": (_sz, [_i, _i, _i]),
-    "tdssf_fusion_fwd": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "tdssf_fusion_fwd": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "tdssf_mlp_fwd_tc": (_i, [_p, _p, _i64, _p, _p, _p, _p, _p]),
     "tdssf_mlp_bwd_tc_workspace_bytes": (_sz, [_i64]),
-    "tdssf_mlp_bwd_tc": (_i, [_p, _p, _p, _p, _p, _i64, C.POINTER(MlpWeights), C.POINTER(MlpGrads), _p, _p, _sz, _p]),
+    "tdssf_mlp_bwd_tc": (_i, [_p, _p, _p, _p, _p, _p, _i64, C.POINTER(MlpWeights), C.POINTER(MlpGrads), _p, _p, _sz, _p]),
     "tdssf_devox_nn_workspace_bytes": (_sz, [_i, _i, _i]),
     "tdssf_devox_nn": (_i, [_p, _i64, _p, _i64, _i, _i, _i, _p, _f, _p, _sz, _p]),
     "tdssf_devox_gather": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),

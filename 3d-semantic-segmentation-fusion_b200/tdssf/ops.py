@@ -250,7 +250,7 @@ class _MlpTC(torch.autograd.Function):
         work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         w = _weights_struct([W1, b1, W2, b2, W3, b3])
         g = _lib.MlpGrads(*[t.data_ptr() for t in grads])
-        check(lib.tdssf_mlp_bwd_tc(_ptr(xp), _ptr(xi), _ptr(h1), _ptr(h2), _ptr(dl), N, C.byref(w), C.byref(g),
+        check(lib.tdssf_mlp_bwd_tc(_ptr(xp), _ptr(xi), None, _ptr(h1), _ptr(h2), _ptr(dl), N, C.byref(w), C.byref(g),
                                    _ptr(dx_pt), _ptr(work), ws_bytes, _stream(xp)), "tdssf_mlp_bwd_tc")
         return (dx_pt.reshape(ctx.in_shape) if dx_pt is not None else None, None, *grads)
 
@@ -273,9 +273,13 @@ def _fusion_workspace(device, B, V, tok_code):
     return ws
 
 
-def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None, preds_out=None):
+def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None, preds_out=None,
+               save=None):
     """Fully fused inference: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) -> logits (B,V,16).
-    preds_out: optional CUDA int64 (B,V) that receives argmax(logits)+1 (class ids 1..16) from the same launch."""
+    preds_out: optional CUDA int64 (B,V) that receives argmax(logits)+1 (class ids 1..16) from the same launch.
+    save: optional (x, h1, h2) contiguous CUDA bf16 tensors of B*V rows x 448 / 256 / 64 that receive the MLP
+    input rows [x_pt | masked camera mean] and the two hidden activations as the tensor cores saw them (for the
+    backward pass, `fusion_train`)."""
     _need_cuda(points, K, Rt, img_hw, tokens, x_pt, packed)
     pts, ss, ps = _points_layout(points)
     B, V, _ = pts.shape
@@ -289,12 +293,63 @@ def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=Fa
     if preds_out is not None and (preds_out.dtype != torch.int64 or not preds_out.is_cuda or preds_out.numel() != B * V
                                   or not preds_out.is_contiguous()):
         raise ValueError("preds_out must be a contiguous CUDA int64 tensor with B*V elements")
+    sx, sh1, sh2 = save if save is not None else (None, None, None)
+    for t, c in ((sx, 448), (sh1, 256), (sh2, 64)):
+        if t is not None and (t.dtype != torch.bfloat16 or not t.is_cuda or not t.is_contiguous()
+                              or t.numel() != B * V * c):
+            raise ValueError(f"save tensors must be contiguous CUDA bf16 with B*V x {c} elements")
     ws = _fusion_workspace(pts.device, B, V, _TOK_DTYPES[tokens.dtype])
     check(lib.tdssf_fusion_fwd(_ptr(pts), ss, ps, _ptr(_f32c(K)), _ptr(_f32c(Rt)), _ptr(_f32c(img_hw)), B, V, NC,
                                int(encoder.resize_height), int(encoder.resize_width), int(encoder.patch_size),
                                _ptr(tokens), _TOK_DTYPES[tokens.dtype], M, Ci, _ptr(xp), _ptr(packed), _ptr(logits),
-                               _ptr(rec), _ptr(preds_out), _ptr(ws), ws.numel(), _stream(pts)), "tdssf_fusion_fwd")
+                               _ptr(rec), _ptr(preds_out), _ptr(sx), _ptr(sh1), _ptr(sh2), _ptr(ws), ws.numel(),
+                               _stream(pts)), "tdssf_fusion_fwd")
     return (logits, rec) if want_rec else logits
+
+
+class _FusedTrain(torch.autograd.Function):
+    """Training through the fused launch: projection, token gather, camera mean and the three layers in one
+    kernel that also writes the bf16 MLP input rows and hidden activations; backward = tdssf_mlp_bwd_tc on those
+    (no fp32 image feature, no concat pass).  Differentiable w.r.t. x_pt and the six parameters; the tokens come
+    from the frozen encoder (reference utils/fusion_model.py:68, torch.no_grad) and get no gradient."""
+
+    @staticmethod
+    def forward(ctx, x_pt, W1, b1, W2, b2, W3, b3, points, K, Rt, img_hw, encoder, tokens):
+        params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
+        _weights_struct(params)  # shape check
+        packed = pack_weights(*params)
+        B, V = x_pt.shape[0], x_pt.shape[1]
+        N = B * V
+        dev = x_pt.device
+        xb = torch.empty((N, 448), dtype=torch.bfloat16, device=dev)
+        h1 = torch.empty((N, 256), dtype=torch.bfloat16, device=dev)
+        h2 = torch.empty((N, 64), dtype=torch.bfloat16, device=dev)
+        logits = fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt.detach(), packed, save=(xb, h1, h2))
+        ctx.save_for_backward(xb, h1, h2, *params)
+        ctx.in_shape = tuple(x_pt.shape)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        xb, h1, h2, W1, b1, W2, b2, W3, b3 = ctx.saved_tensors
+        N = xb.shape[0]
+        dev = xb.device
+        dl = _f32c(dlogits).reshape(-1, 16)
+        grads = [torch.zeros_like(t) for t in (W1, b1, W2, b2, W3, b3)]
+        dx_pt = torch.empty((N, 64), dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
+        ws_bytes = lib.tdssf_mlp_bwd_tc_workspace_bytes(N)
+        work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        w = _weights_struct([W1, b1, W2, b2, W3, b3])
+        g = _lib.MlpGrads(*[t.data_ptr() for t in grads])
+        check(lib.tdssf_mlp_bwd_tc(None, None, _ptr(xb), _ptr(h1), _ptr(h2), _ptr(dl), N, C.byref(w), C.byref(g),
+                                   _ptr(dx_pt), _ptr(work), ws_bytes, _stream(xb)), "tdssf_mlp_bwd_tc")
+        return (dx_pt.reshape(ctx.in_shape) if dx_pt is not None else None, *grads, None, None, None, None, None, None)
+
+
+def fusion_train(points, K, Rt, img_hw, encoder, tokens, x_pt, W1, b1, W2, b2, W3, b3):
+    """Fused forward with a bf16 tensor-core backward: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) ->
+    logits (B,V,16), differentiable w.r.t. x_pt and the six MLP parameters (1e-2 tolerance)."""
+    return _FusedTrain.apply(x_pt, W1, b1, W2, b2, W3, b3, points, K, Rt, img_hw, encoder, tokens)
 
 
 # ------------------------------------------------------------------------------------------------

@@ -9,8 +9,8 @@ Reference interface mirrored (file:line in the reference tree):
                  cam_intrinsics, lidar2cam_extrinsics) -> point_scores                        :152-207
 
 MLP arithmetic is selected with the environment variable TDSSF_MLP:
-    bf16 (default)  inference through the fully fused tcgen05 kernel; when a gradient is required: projection + gather
-                    kernels, tcgen05 forward that saves its bf16 activations, bf16 backward (1e-2 tolerance, north_star)
+    bf16 (default)  the fully fused tcgen05 kernel; when a gradient is required the same launch also saves its bf16
+                    input rows and activations and the backward runs in bf16 (1e-2 tolerance, north_star)
     fp32            fp32 CUDA-core kernels everywhere (1e-5 tolerance)
 """
 from __future__ import annotations
@@ -121,16 +121,17 @@ class FeatureFusionModel(nn.Module):
         if mode not in ("bf16", "fp32"):
             raise ValueError(f"TDSSF_MLP must be bf16 or fp32, got {mode!r}")
 
-        if mode == "bf16" and not needs_grad and dim == 384 and self.mlp[0].in_features == 448:
+        fused_ok = mode == "bf16" and dim == 384 and self.mlp[0].in_features == 448
+        if fused_ok and not needs_grad:
             voxel_scores = ops.fusion_fwd(voxel_raw, K, Rt, hw, enc, tokens, voxel_features, self._packed_weights())
+        elif fused_ok:
+            # training: the same fused launch, saving its bf16 input rows and activations for the backward pass
+            voxel_scores = ops.fusion_train(voxel_raw, K, Rt, hw, enc, tokens, voxel_features, *params)
         else:
             rec = ops.project(voxel_raw, K, Rt, hw, enc, want_pix=False, want_depth=False, want_valid=False,
                               want_rec=True)["rec"]
             fused_img_feat = ops.gather_mean(tokens, rec)
-            if mode == "bf16" and dim == 384 and self.mlp[0].in_features == 448:
-                voxel_scores = ops.mlp_tc_train(voxel_features, fused_img_feat, *params)   # training, tensor cores
-            else:
-                voxel_scores = ops.mlp_f32(voxel_features, fused_img_feat, *params)
+            voxel_scores = ops.mlp_f32(voxel_features, fused_img_feat, *params)
 
         point_scores, _ = self.pcd_encoder.devoxelize(voxel_scores)
         return point_scores

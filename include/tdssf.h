@@ -154,6 +154,9 @@ TDSSF_API int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w_host, void* pack
  * x_pt    [B*V,64] fp32 point features (PTv3 output)
  * logits  [B*V,16] fp32
  * rec_out optional [B,V] camera-assignment records (NULL to skip).
+ * x_bf16 / h1_bf16 / h2_bf16  optional (NULL to skip; training): [B*V,448] the MLP input rows [point feature | image
+ *          feature] and [B*V,256] / [B*V,64] the post-ReLU activations, all in bf16 exactly as the tensor cores consumed
+ *          them - what tdssf_mlp_bwd_tc needs, so that training never materialises the fp32 image feature either.
  * preds_out optional [B*V] int64 class ids = argmax(logits) + 1 (first maximum, like torch.argmax; utils/losses.py:66),
  *          for the evaluation loop's confusion matrix (NULL to skip).
  * workspace: tdssf_fusion_workspace_bytes(B, V, tok_dtype) bytes, 256-byte aligned.  Holds, per point, the address of
@@ -167,6 +170,7 @@ TDSSF_API int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t p
                      const void* tokens, int tok_dtype, int M, int Ci,
                      const float* x_pt, const void* packed_weights,
                      float* logits, tdssf_rec* rec_out, int64_t* preds_out,
+                     void* x_bf16, void* h1_bf16, void* h2_bf16,
                      void* workspace, size_t workspace_bytes, void* stream);
 
 /* tensor-core MLP on pre-gathered features (training forward, and the unfused check of the fused kernel).
@@ -177,12 +181,13 @@ TDSSF_API int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N,
 
 /* bf16 backward of the MLP from the activations tdssf_mlp_fwd_tc saved (training with the tensor-core forward).
  * replaces  the autograd of FeatureFusionModel.mlp   utils/fusion_model.py:144-150,203-204 (utils/train.py:91)
+ * The input rows come either as x_bf16 [N,448] (saved by tdssf_fusion_fwd) or, when x_bf16 is NULL, as fp32 x_pt / x_img.
  * Accumulates (+=) dW*, db* into the caller's fp32 buffers (zeroed by the caller) and writes dx_pt [N,64] (may be NULL).
  * The six products are plain GEMMs and run in cuBLAS (bf16 operands, fp32 accumulate), loaded at first use; the
  * conversions, ReLU masks and bias-gradient sums are kernels of this library.  TDSSF_ENOSUP if cuBLAS cannot be loaded.
  * workspace: tdssf_mlp_bwd_tc_workspace_bytes(N), 256-byte aligned. */
 TDSSF_API size_t tdssf_mlp_bwd_tc_workspace_bytes(int64_t N);
-TDSSF_API int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* h1_bf16, const void* h2_bf16,
+TDSSF_API int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* x_bf16, const void* h1_bf16, const void* h2_bf16,
                      const float* dlogits, int64_t N, const tdssf_mlp_weights* w_host,
                      const tdssf_mlp_grads* g_host, float* dx_pt,
                      void* workspace, size_t workspace_bytes, void* stream);

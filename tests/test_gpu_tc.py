@@ -257,6 +257,64 @@ def test_mlp_tc_training_gradients(ops):
         assert rel(a, b) < 0.1, (k, rel(a, b))   # random upstream gradient: no mean component to average the flips out
 
 
+def test_fused_training_saved_rows_and_gradients(ops):
+    """Training through the fused launch (ops.fusion_train).  The rows it saves for the backward pass are bit-exactly
+    bf16([x_pt | masked camera mean]) of the stand-alone projection + gather kernels for single-camera points (a plain
+    copy of one token row) and within one bf16 ulp for points seen by several cameras (the fused kernel averages in a
+    different order); logits equal the inference launch bit for bit; gradients match the unfused tensor-core path."""
+    B, V = 3, 7001   # not a multiple of the 256-row tile: the last tile is ragged
+    sw = synth.make_sweeps(B, V, "dinov3", seed=41)
+    w = synth.make_mlp_weights(41)
+    K, Rt, hw = torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda()
+    pts, tok, xp = sw.points.cuda(), sw.tokens.cuda(), sw.point_feat.cuda()
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    N = B * V
+    xb = torch.full((N, 448), float("nan"), dtype=torch.bfloat16, device="cuda")
+    h1 = torch.full((N, 256), float("nan"), dtype=torch.bfloat16, device="cuda")
+    h2 = torch.full((N, 64), float("nan"), dtype=torch.bfloat16, device="cuda")
+    logits, rec = ops.fusion_fwd(pts, K, Rt, hw, sw.encoder, tok, xp, packed, want_rec=True, save=(xb, h1, h2))
+    plain = ops.fusion_fwd(pts, K, Rt, hw, sw.encoder, tok, xp, packed)
+    assert torch.equal(logits, plain)
+    feat = ops.gather_mean(tok, rec)
+    want = torch.cat([xp.reshape(N, 64), feat.reshape(N, 384)], -1).bfloat16()
+    assert not torch.isnan(xb.float()).any() and not torch.isnan(h1.float()).any() and not torch.isnan(h2.float()).any()
+    assert torch.equal(xb[:, :64], want[:, :64])
+    single = ops.project(pts, K, Rt, hw, sw.encoder, want_pix=False, want_depth=False, want_rec=False)["valid"].sum(1).reshape(-1) <= 1
+    assert int(single.sum()) > N // 4
+    assert torch.equal(xb[single], want[single])
+    d = (xb.float() - want.float()).abs()
+    assert float((d / want.float().abs().clamp_min(1e-3)).max()) < 2 ** -7   # one bf16 ulp
+    # hidden activations against a model of the kernel fed with the saved rows
+    q = lambda t: t.bfloat16().double()
+    m1 = torch.relu(xb.double() @ q(wd[0]).T + wd[1].double())
+    assert float((h1.double() - m1).abs().max() / m1.abs().max()) < 1e-2
+    m2 = torch.relu(h1.double() @ q(wd[2]).T + wd[3].double())
+    assert float((h2.double() - m2).abs().max() / m2.abs().max()) < 1e-2
+
+    # gradients: fused training path against the unfused tensor-core path (same arithmetic up to the mean's rounding)
+    dl = torch.randn(B, V, 16, generator=torch.Generator().manual_seed(5)).cuda()
+
+    def run(fused):
+        params = [t.clone().requires_grad_(True) for t in wd]
+        x = xp.clone().requires_grad_(True)
+        if fused:
+            out = ops.fusion_train(pts, K, Rt, hw, sw.encoder, tok, x, *params)
+        else:
+            out = ops.mlp_tc_train(x, feat, *params)
+        out.backward(dl)
+        return out.detach(), x.grad, [p.grad for p in params]
+
+    out_a, dx_a, g_a = run(True)
+    out_b, dx_b, g_b = run(False)
+    rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm())
+    assert torch.equal(out_a, logits)
+    assert rel(out_a, out_b) < 2e-3
+    assert dx_a.shape == xp.shape and rel(dx_a, dx_b) < 1e-2
+    for k, a, b in zip(W_KEYS, g_a, g_b):
+        assert rel(a, b) < 1e-2, (k, rel(a, b))
+
+
 def test_dropin_training_step_bf16(ops, monkeypatch):
     """FeatureFusionModel in training mode with the default (bf16) arithmetic: loss and parameter gradients against
     TDSSF_MLP=fp32 on the same inputs."""

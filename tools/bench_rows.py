@@ -194,8 +194,8 @@ emit("config3", "training step per GPU, TDSSF_MLP=fp32 (drop-in modules: forward
      note="4 sweeps x 34 720 points; project + gather + fp32 MLP fwd, cels fwd/bwd, fp32 MLP bwd; no optimizer, no all-reduce")
 os.environ["TDSSF_MLP"] = "bf16"
 ms = timeit(train_step, n=5)
-emit("config3", "training step per GPU, default bf16 (tcgen05 forward, bf16 backward with cuBLAS GEMMs)", ms, Bt * V, "points",
-     note="4 sweeps x 34 720 points; project + gather + tcgen05 MLP fwd saving bf16 activations, cels fwd/bwd, bf16 backward")
+emit("config3", "training step per GPU, default bf16 (fused tcgen05 forward, bf16 backward with cuBLAS GEMMs)", ms, Bt * V, "points",
+     note="4 sweeps x 34 720 points; fused launch saving its bf16 input rows + activations, cels fwd/bwd, bf16 backward")
 wt = [t.clone().requires_grad_(True) for t in wd]
 featt = feat.clone().requires_grad_(True)
 
@@ -211,6 +211,19 @@ def mlp_tc_train_step():
 ms = timeit(mlp_tc_train_step, n=5)
 emit("a6", "mlp_fwd_tc (saving h1/h2) + mlp_bwd_tc", ms, N, "points", flops_per_unit=3 * flops - 2 * 384 * 256,
      note="8 sweeps; bf16 tensor-core forward + bf16 backward (cuBLAS GEMMs, own element-wise kernels); frac is against the fp32 FMA peak for comparison with the fp32 row")
+
+
+def fused_train_step():
+    o = ops.fusion_train(pts, K, Rt, hw, enc, tok, featt, *wt)
+    o.backward(torch.ones_like(o))
+    for t in wt:
+        t.grad = None
+    featt.grad = None
+
+
+ms = timeit(fused_train_step, n=5)
+emit("a1-a6", "fusion_fwd (saving x/h1/h2) + mlp_bwd_tc", ms, N, "points", flops_per_unit=3 * flops - 2 * 384 * 256,
+     note="8 sweeps; the fused launch also writes its bf16 input rows; backward reads them (no fp32 image feature, no concat)")
 
 # configs[4]: evaluation step: fused inference + argmax + confusion accumulation (8 sweeps)
 cm.zero_()
