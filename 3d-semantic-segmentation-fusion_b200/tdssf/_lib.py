@@ -29,7 +29,7 @@ if not os.path.exists(LIB_PATH):
 
 lib = C.CDLL(LIB_PATH)
 
-_p, _i, _i64, _sz, _f = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
+_p, _i, _i64, _sz, _f, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_double
 
 # name -> (restype, argtypes); kept in one table so tests can check it against include/tdssf.h
 SIGNATURES = {
@@ -49,6 +49,8 @@ SIGNATURES = {
     "tdssf_mlp_fwd_tc": (_i, [_p, _p, _i64, _p, _p, _p, _p, _p]),
     "tdssf_mlp_bwd_tc_workspace_bytes": (_sz, [_i64]),
     "tdssf_mlp_bwd_tc": (_i, [_p, _p, _p, _p, _p, _p, _i64, C.POINTER(MlpWeights), C.POINTER(MlpGrads), _p, _p, _sz, _p]),
+    "tdssf_voxelize_workspace_bytes": (_sz, [_i, _i]),
+    "tdssf_voxelize": (_i, [_p, _i64, _i, _i, _i, _d, _d, _p, _p, _p, _p, _p, _sz, _p]),
     "tdssf_devox_nn_workspace_bytes": (_sz, [_i, _i, _i]),
     "tdssf_devox_nn": (_i, [_p, _i64, _p, _i64, _i, _i, _i, _p, _f, _p, _sz, _p]),
     "tdssf_devox_gather": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),

@@ -353,6 +353,37 @@ def fusion_train(points, K, Rt, img_hw, encoder, tokens, x_pt, W1, b1, W2, b2, W
 
 
 # ------------------------------------------------------------------------------------------------
+# f1
+# ------------------------------------------------------------------------------------------------
+_voxel_ws: dict = {}
+
+
+def voxelize(points: torch.Tensor, voxel_size: float, knn_cell: Optional[float] = None):
+    """points (B,P,3|4) CUDA fp32 -> voxel_raw (B,P,4) fp32 [centroid xyz, 5-NN weighted intensity] with the rows past
+    each cloud's voxel count zeroed, voxel_coords (B,P,3) int32, n_voxels (B,) int32 (utils/lidar.py:83-118 for B
+    clouds in one call; voxels in the order of their first point).  Nothing is read back to the host."""
+    _need_cuda(points)
+    pts = _f32c(points)
+    if pts.dim() != 3 or pts.shape[-1] < 3:
+        raise ValueError("points must have shape (B, P, >=3)")
+    B, P, st = pts.shape
+    dev = pts.device
+    raw = torch.empty((B, P, 4), dtype=torch.float32, device=dev)
+    coords = torch.empty((B, P, 3), dtype=torch.int32, device=dev)
+    n_vox = torch.zeros((B,), dtype=torch.int32, device=dev)
+    status = torch.zeros((1,), dtype=torch.int32, device=dev)
+    need = lib.tdssf_voxelize_workspace_bytes(B, P)
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _voxel_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        _voxel_ws[key] = ws
+    check(lib.tdssf_voxelize(_ptr(pts), st, B, P, int(st >= 4), float(voxel_size), float(knn_cell or 0.0), _ptr(raw),
+                             _ptr(coords), _ptr(n_vox), _ptr(status), _ptr(ws), ws.numel(), _stream(pts)), "tdssf_voxelize")
+    return raw, coords, n_vox, status
+
+
+# ------------------------------------------------------------------------------------------------
 # a7
 # ------------------------------------------------------------------------------------------------
 _devox_ws: dict = {}

@@ -2,9 +2,11 @@
 
 In scope here: the padding / caching contract of `forward` and `devoxelize` (nearest voxel per raw
 point, gather, differentiable through the gathered scores), which runs on libtdssf.so
-(csrc/devox.cu).  The PTv3 backbone and the Open3D voxelizer stay stock third-party code exactly as
-in the reference: they are imported lazily, and a caller may inject replacements (`backbone=`,
-`voxelizer=`) — the synthetic harness does, because neither open3d nor spconv exists in this image.
+(csrc/devox.cu), and the voxelizer (csrc/voxel.cu: the Open3D down-sampling + scikit-learn 5-NN of
+utils/lidar.py:83-118 without leaving the device; `voxelizer="open3d"` selects the stock host path).
+The PTv3 backbone stays stock third-party code exactly as in the reference: it is imported lazily,
+and a caller may inject a replacement (`backbone=`) — the synthetic harness does, because spconv
+does not exist in this image.
 """
 from __future__ import annotations
 
@@ -63,9 +65,18 @@ class LiDARFeatureEncoder(nn.Module):
 
     def voxelize_open3d(self, lidar_points):
         """(P,4) -> voxel_raw (V,4) [centroid xyz, 5-NN weighted intensity], voxel_coords (V,3) int32.
-        Stock Open3D + scikit-learn like the reference (utils/lidar.py:83-118) unless a voxelizer was injected."""
-        if self._voxelizer is not None:
+        On the device by default; `voxelizer="open3d"` = stock Open3D + scikit-learn like the reference
+        (utils/lidar.py:83-118); a callable `voxelizer(points, voxel_size)` replaces both."""
+        if callable(self._voxelizer):
             return self._voxelizer(lidar_points, self.voxel_size)
+        if self._voxelizer != "open3d":   # default: on the device (csrc/voxel.cu), voxels in order of their first point
+            if lidar_points.shape[1] == 4 and lidar_points.shape[0] < 5:
+                raise ValueError("Expected n_neighbors <= n_samples_fit")   # what scikit-learn raises at :99
+            raw, coords, n_vox, status = ops.voxelize(lidar_points.detach()[None], self.voxel_size)
+            n, bad = int(n_vox[0]), int(status[0])   # the one host read of the step (the reference syncs on .cpu())
+            if bad:
+                raise RuntimeError("voxelize: non-finite coordinates or more than 2^21 voxels along an axis")
+            return raw[0, :n, :lidar_points.shape[1]], coords[0, :n]
         try:
             import open3d as o3d
             from sklearn.neighbors import NearestNeighbors

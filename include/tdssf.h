@@ -214,6 +214,27 @@ TDSSF_API int tdssf_devox_scatter_add(const float* dout, const int64_t* idx, int
                             float* dscores, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * f1  voxelizer: voxel down-sampling + 5-NN weighted intensity + grid coordinates, on the device
+ * replaces  LiDARFeatureEncoder.voxelize_open3d   utils/lidar.py:83-118  (Open3D voxel_down_sample on the host,
+ *           scikit-learn NearestNeighbors(5), numpy) for B clouds at once.
+ * pts [B,P,point_stride_floats] fp32 (xyz first, intensity at column 3 when has_intensity).
+ * voxel_raw [B,P,4] fp32: rows 0..n_voxels[b]-1 = (centroid xyz, weighted intensity), the rest zero padding.
+ * voxel_coords [B,P,3] int32 = floor(centroid / voxel_size).  n_voxels [B] int32 (device).
+ * Arithmetic follows Open3D 0.18 (all in double on the fp32 coordinates: voxel index
+ * int(floor((p - (min_bound - voxel_size/2)) / voxel_size)), points accumulated in point order, sum / count) and the
+ * reference's numpy (intensity = sum_k I[nbr_k] * {0.4,0.3,0.2,0.05,0.05}[k] in double, nearest first; equidistant
+ * neighbours: lower point index first, where scikit-learn's order is unspecified).  Voxels come in the order of their
+ * first point (Open3D: unordered_map iteration order).  knn_cell: edge of the neighbour-search grid cells, any
+ * positive value gives the same result; <= 0 selects max(2*voxel_size, 0.25).
+ * status (optional, device int32): bit 0 set when a coordinate was not finite or an axis spans more than 2^21 voxels
+ * (results undefined then).  Errors: TDSSF_EINVAL for voxel_size <= 0 or has_intensity with P < 5 (the reference
+ * raises in both cases). */
+TDSSF_API size_t tdssf_voxelize_workspace_bytes(int B, int P);
+TDSSF_API int tdssf_voxelize(const float* pts, int64_t point_stride_floats, int B, int P, int has_intensity,
+                   double voxel_size, double knn_cell, float* voxel_raw, int32_t* voxel_coords, int32_t* n_voxels,
+                   int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * a8+a9+a10  CE + Lovasz-Softmax loss, forward and backward in one call
  * replaces  CELSLoss.forward            utils/losses.py:19-70
  *           lovasz_softmax_flat         LovaszSoftmax/pytorch/lovasz_losses.py:171-199

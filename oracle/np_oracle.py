@@ -389,3 +389,80 @@ def precision_recall_f1(cm):
     recall = (tp / np.maximum(tp + fn, F32(1))).mean(dtype=np.float32)
     f1 = F32(2) * precision * recall / max(precision + recall, F32(1e-6))
     return precision, recall, f1
+
+
+# ------------------------------------------------------------------------------------------------
+# f1  voxelize_open3d                                           utils/lidar.py:83-118
+#
+# PARITY UNPINNED for the down-sampling step: it lives in Open3D (pinned 0.18.0, environment.yml:278), which is
+# neither under the reference tree nor installed here.  Restated from its published algorithm
+# (geometry::PointCloud::VoxelDownSample, cpp/open3d/geometry/PointCloud.cpp): all arithmetic in double on the
+# fp32 coordinates; voxel_min_bound = min_bound - voxel_size/2; voxel index = int(floor((p - voxel_min_bound) /
+# voxel_size)) per axis; per occupied voxel the points are accumulated in point order and divided by their count.
+# Open3D emits the voxels in the iteration order of a std::unordered_map (implementation-defined); here they come
+# in the order of the first point of each voxel, so comparisons with Open3D itself would be as sets.
+# The 5-NN intensity step is scikit-learn (installed here: `voxelize(..., knn="sklearn")` runs the reference's own
+# call) and numpy; `knn="brute"` restates it (exact double squared distances, ties to the lower point index).
+# ------------------------------------------------------------------------------------------------
+KNN_WEIGHTS = np.array([0.4, 0.3, 0.2, 0.05, 0.05])
+
+
+def voxel_down_sample(xyz, voxel_size):
+    """xyz (P,3) fp32 -> centroids (V,3) float64 in order of first appearance, plus per-point voxel id (P,)."""
+    pts = np.asarray(xyz, dtype=F32).astype(np.float64)
+    vmin = pts.min(axis=0) - np.float64(voxel_size) * 0.5
+    vidx = np.floor((pts - vmin) / np.float64(voxel_size)).astype(np.int64)
+    _, first, inv = np.unique(vidx, axis=0, return_index=True, return_inverse=True)
+    inv = inv.reshape(-1)
+    order = np.argsort(first, kind="stable")            # voxels by their first point
+    rank = np.empty_like(order)
+    rank[order] = np.arange(order.size)
+    vid = rank[inv]
+    sums = np.zeros((order.size, 3), dtype=np.float64)
+    np.add.at(sums, vid, pts)                            # unbuffered: accumulates in point order, like AddPoint
+    cnt = np.bincount(vid, minlength=order.size).astype(np.float64)
+    return sums / cnt[:, None], vid
+
+
+def knn5_brute(xyz, queries, chunk=512):
+    """Indices (V,5) of the five nearest points per query, nearest first; double squared distances
+    ((dx*dx + dy*dy) + dz*dz), ties to the lower index; also the gap d2[5] - d2[4] to the sixth neighbour."""
+    pts = np.asarray(xyz, dtype=F32).astype(np.float64)
+    out = np.empty((queries.shape[0], 5), dtype=np.int64)
+    gap = np.full(queries.shape[0], np.inf)
+    mingap = np.full(queries.shape[0], np.inf)
+    for s in range(0, queries.shape[0], chunk):
+        q = queries[s:s + chunk]
+        d = q[:, None, :] - pts[None, :, :]
+        d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
+        k = min(6, pts.shape[0])
+        part = np.argpartition(d2, k - 1, axis=1)[:, :k]
+        pd = np.take_along_axis(d2, part, axis=1)
+        o = np.lexsort((part, pd), axis=1)               # by distance, then by index
+        part = np.take_along_axis(part, o, axis=1)
+        pd = np.take_along_axis(pd, o, axis=1)
+        out[s:s + chunk] = part[:, :5]
+        if k == 6:
+            gap[s:s + chunk] = pd[:, 5] - pd[:, 4]
+        mingap[s:s + chunk] = np.diff(pd[:, :k], axis=1).min(axis=1)
+    return out, gap, mingap
+
+
+def voxelize(points, voxel_size, knn="brute"):
+    """points (P,4) fp32 [x y z intensity] -> voxel_raw (V,4) fp32, voxel_coords (V,3) int32, following
+    utils/lidar.py:83-118 step by step (Step 2 per the note above).  Extra returns for the tests: per-point voxel
+    id and the smallest distance gap among each voxel's six nearest points (0 = a tie: neighbour order undefined)."""
+    pts = np.asarray(points, dtype=F32)
+    centres, vid = voxel_down_sample(pts[:, :3], voxel_size)             # :92-93
+    if pts.shape[1] < 4:                                                  # :104-105: no intensity column
+        return centres.astype(F32), np.floor(centres / voxel_size).astype(np.int32), vid, None
+    if knn == "sklearn":
+        from sklearn.neighbors import NearestNeighbors
+        _, idx = NearestNeighbors(n_neighbors=5, algorithm="auto").fit(pts[:, :3]).kneighbors(centres)   # :98-99
+        mingap = None
+    else:
+        idx, _, mingap = knn5_brute(pts[:, :3], centres)
+    inten = (pts[idx, 3] * KNN_WEIGHTS.reshape(1, 5)).sum(axis=1).reshape(-1, 1)                        # :101-102
+    raw = np.hstack([centres, inten])                                                                   # :103
+    coords = np.floor(centres / voxel_size).astype(np.int32)                                            # :108-110
+    return raw.astype(F32), coords, vid, mingap                                                         # :113-114

@@ -242,3 +242,17 @@ def eval_step():
 ms = timeit(eval_step)
 emit("config5", "evaluation step per GPU (fused forward with class ids + confusion)", ms, N, "points",
      note="8 sweeps x 34 720 points; two launches, the arg-max comes out of the fused kernel's last epilogue")
+
+# f1: voxelizer on the device (8 sweeps, voxel 0.1 and 0.5 m) next to the reference's host path (Open3D restated in
+# numpy + the reference's own scikit-learn call) on ONE sweep on this box's cores
+import time
+from oracle import np_oracle as O
+for vs in (0.1, 0.5):
+    ms = timeit(lambda: ops.voxelize(pts, vs))
+    one = pts[0].cpu().numpy()
+    t0 = time.perf_counter()
+    O.voxelize(one, vs, knn="sklearn")
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    emit("f1", f"tdssf_voxelize, voxel {vs} m", ms, N, "points",
+         note=f"8 sweeps x 34 720 points in one call (down-sample + 5-NN intensity + coords); host path (numpy restatement of Open3D "
+              f"+ scikit-learn KD-tree) on one sweep: {cpu_ms:.1f} ms = {V / cpu_ms * 1e3:.3g} points/s")
