@@ -32,12 +32,19 @@ constexpr int kAxisBits = 21;              // packed voxel index: 3 x 21 bits
 constexpr unsigned long long kEmpty = ~0ull;
 constexpr int kK = 5;
 constexpr int kLevels = 6;                 // neighbour grids: cell, 2 cell, ... 32 cell
+#ifndef TDSSF_VOX_START
+#define TDSSF_VOX_START 48
+#endif
+// the search starts at the finest grid whose 27 buckets around the centre hold this many points: with n points in the
+// 27 c^3 cube about n/6.4 lie within the 0.99 c ball that certifies the result, so 48 makes a second walk rare
+constexpr int kStartCount = TDSSF_VOX_START;
 
 struct Ws {
   int* bounds;          // [B][4]  ordered-int encoding of the min corner (init: large)
   int* first;           // [B][T]  lowest point index per table slot (init: large)
   unsigned long long* keys;  // [B][T] packed voxel index (init: empty)
   int* head;            // [kLevels][B][T]  neighbour-grid bucket heads (init: -1)
+  int* cnt;             // [kLevels][B][T]  points per bucket (init: 0)
   int* next;            // [kLevels][B][P]  neighbour-grid links
   int* slot;            // [B][P]  table slot of every point
   int* slot_rank;       // [B][T]  voxel number per table slot
@@ -68,6 +75,7 @@ static size_t carve(Ws* ws, char* base, int B, int P) {
   p = take((size_t)B * T * 8); if (ws) ws->keys = (unsigned long long*)p;    // 0xff region
   p = take((size_t)kLevels * B * T * 4); if (ws) ws->head = (int*)p;
   p = take(256); if (ws) ws->counters = (int*)p;                             // 0x00 region
+  p = take((size_t)kLevels * B * T * 4); if (ws) ws->cnt = (int*)p;
   p = take((size_t)kLevels * B * P * 4); if (ws) ws->next = (int*)p;
   p = take((size_t)B * P * 4); if (ws) ws->slot = (int*)p;
   p = take((size_t)B * T * 4); if (ws) ws->slot_rank = (int*)p;
@@ -159,6 +167,7 @@ insert_kernel(const float* __restrict__ pts, int64_t stride, int P, int B, doubl
   for (int l = 0; l < kLevels; ++l, inv *= 0.5) {
     const uint32_t h = cell_hash(cell_of(x, inv), cell_of(y, inv), cell_of(z, inv)) & mask;
     ws.next[((size_t)l * B + b) * P + i] = atomicExch(ws.head + ((size_t)l * B + b) * T + h, i);
+    atomicAdd(ws.cnt + ((size_t)l * B + b) * T + h, 1);
   }
 }
 
@@ -462,7 +471,22 @@ knn_grid_kernel(const float* __restrict__ pts, int64_t stride, int P, int B, dou
     double d[kK];
     int nb[kK];
     bool done = false;
-    int l = 0;
+    // bucket counts of all grids: one round of independent loads instead of walking the lists of grids that are too fine
+    // (or too coarse) for this neighbourhood
+    int l = kLevels - 1;
+    {
+      int c[kLevels];
+#pragma unroll
+      for (int k = 0; k < kLevels; ++k) {
+        const double inv = (1.0 / cell) / (double)(1 << k);
+        const int tx = cell_of(qx, inv) + lane % 3 - 1, ty = cell_of(qy, inv) + (lane / 3) % 3 - 1, tz = cell_of(qz, inv) + lane / 9 - 1;
+        c[k] = lane < 27 ? ws.cnt[((size_t)k * B + b) * T + (cell_hash(tx, ty, tz) & mask)] : 0;
+      }
+#pragma unroll
+      for (int k = kLevels - 1; k >= 0; --k) {
+        if (__reduce_add_sync(0xffffffffu, c[k]) >= kStartCount) l = k;
+      }
+    }
     while (l < kLevels) {
       const double c = cell * (double)(1 << l), inv = (1.0 / cell) / (double)(1 << l);   // powers of two: exact, as in insert_kernel
       const int* head = ws.head + ((size_t)l * B + b) * T;
@@ -565,7 +589,7 @@ extern "C" int tdssf_voxelize(const float* pts, int64_t point_stride_floats, int
   const int tiles = (int)ceil_div(P, kTile), stiles = (int)ceil_div(P, kSortTile);
   TDSSF_CUDA(cudaMemsetAsync(ws.bounds, 0x7f, (char*)ws.keys - (char*)ws.bounds, s));
   TDSSF_CUDA(cudaMemsetAsync(ws.keys, 0xff, (char*)ws.counters - (char*)ws.keys, s));
-  TDSSF_CUDA(cudaMemsetAsync(ws.counters, 0, 256, s));
+  TDSSF_CUDA(cudaMemsetAsync(ws.counters, 0, (char*)ws.next - (char*)ws.counters, s));
   const dim3 pgrid((unsigned)tiles, (unsigned)B);
   bounds_kernel<<<pgrid, kTile, 0, s>>>(pts, point_stride_floats, P, ws.bounds);
   TDSSF_LAUNCH_CHECK();

@@ -243,16 +243,19 @@ ms = timeit(eval_step)
 emit("config5", "evaluation step per GPU (fused forward with class ids + confusion)", ms, N, "points",
      note="8 sweeps x 34 720 points; two launches, the arg-max comes out of the fused kernel's last epilogue")
 
-# f1: voxelizer on the device (8 sweeps, voxel 0.1 and 0.5 m) next to the reference's host path (Open3D restated in
-# numpy + the reference's own scikit-learn call) on ONE sweep on this box's cores
+# f1: voxelizer on the device (8 sweeps, voxel 0.1 and 0.5 m).  Beside it, as a LOWER bound of the reference's host path
+# (utils/lidar.py:83-118: D2H copy, Open3D down-sampling, scikit-learn 5-NN, H2D copy), the reference's own scikit-learn
+# call alone on ONE sweep on this box's cores (queries = the device voxelizer's centroids).
 import time
-from oracle import np_oracle as O
+from sklearn.neighbors import NearestNeighbors
 for vs in (0.1, 0.5):
     ms = timeit(lambda: ops.voxelize(pts, vs))
+    raw_v, _, n_v, _ = ops.voxelize(pts, vs)
     one = pts[0].cpu().numpy()
+    cen = raw_v[0, :int(n_v[0]), :3].double().cpu().numpy()
     t0 = time.perf_counter()
-    O.voxelize(one, vs, knn="sklearn")
+    NearestNeighbors(n_neighbors=5, algorithm="auto").fit(one[:, :3]).kneighbors(cen)
     cpu_ms = (time.perf_counter() - t0) * 1e3
     emit("f1", f"tdssf_voxelize, voxel {vs} m", ms, N, "points",
-         note=f"8 sweeps x 34 720 points in one call (down-sample + 5-NN intensity + coords); host path (numpy restatement of Open3D "
-              f"+ scikit-learn KD-tree) on one sweep: {cpu_ms:.1f} ms = {V / cpu_ms * 1e3:.3g} points/s")
+         note=f"8 sweeps x 34 720 points in one call (down-sample + 5-NN intensity + coords), {int(n_v.float().mean())} voxels per sweep; "
+              f"scikit-learn 5-NN alone (part of the reference's host path) on one sweep: {cpu_ms:.1f} ms = {V / cpu_ms * 1e3:.3g} points/s")
