@@ -9,6 +9,7 @@
 //   5. closed-form backward through |.|, the sort permutation, softmax and CE -> dlogits
 // Everything is HBM-bound integer / fp32 work; there is no tensor-core stage.
 #include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace tdssf {
@@ -19,6 +20,8 @@ constexpr int kSortThreads = 256;
 constexpr int kKeysPerThread = 8;
 constexpr int kSortTile = kSortThreads * kKeysPerThread;  // 2048 keys per CTA
 constexpr int kRadixBits = 8, kBins = 1 << kRadixBits, kPasses = 4;
+constexpr int kFusedScanTiles = 256;   // up to this many sort tiles per class the scatter kernel derives its own offsets
+static_assert(kBins == kSortThreads, "one thread per radix bin in the histogram / offset code");
 constexpr uint32_t kOneBits = 0x3F800000u;
 
 struct CelsWs {
@@ -208,7 +211,7 @@ cels_compact_kernel(const float* __restrict__ logits, const int64_t* __restrict_
 // segment yields the global offset of every (bin, tile) pair.
 __global__ void __launch_bounds__(kSortThreads)
 sort_hist_kernel(const uint32_t* __restrict__ keys, int N, int shift, int tiles,
-                 const int* __restrict__ class_count, uint32_t* __restrict__ hist) {
+                 const int* __restrict__ class_count, uint32_t* __restrict__ hist, bool tile_major) {
   const int seg = blockIdx.y, tile = blockIdx.x;
   if (class_count[seg] == 0) return;  // absent class: skipped by classes='present'
   __shared__ uint32_t s_h[kBins];
@@ -222,7 +225,8 @@ sort_hist_kernel(const uint32_t* __restrict__ keys, int N, int shift, int tiles,
     if (idx < N) atomicAdd(&s_h[(k[idx] >> shift) & (kBins - 1)], 1u);
   }
   __syncthreads();
-  hist[((int64_t)seg * kBins + threadIdx.x) * tiles + tile] = s_h[threadIdx.x];
+  if (tile_major) hist[((int64_t)seg * tiles + tile) * kBins + threadIdx.x] = s_h[threadIdx.x];   // raw counts, see sort_scatter_kernel
+  else hist[((int64_t)seg * kBins + threadIdx.x) * tiles + tile] = s_h[threadIdx.x];
 }
 
 // one CTA per segment: in-place exclusive scan over kBins*tiles counters, 8 per thread per step
@@ -254,7 +258,7 @@ sort_scan_kernel(uint32_t* __restrict__ hist, int tiles, const int* __restrict__
 __global__ void __launch_bounds__(kSortThreads)
 sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int N, int shift,
-                    int tiles, const int* __restrict__ class_count, const uint32_t* __restrict__ hist) {
+                    int tiles, const int* __restrict__ class_count, const uint32_t* __restrict__ hist, bool tile_major) {
   const int seg = blockIdx.y, tile = blockIdx.x;
   if (class_count[seg] == 0) return;
   constexpr int kWarps = kSortThreads / 32;
@@ -262,7 +266,24 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   __shared__ uint32_t s_base[kBins];          // global offset of (bin, tile)
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < kWarps * kBins; i += kSortThreads) (&s_cnt[0][0])[i] = 0;
-  s_base[threadIdx.x] = hist[((int64_t)seg * kBins + threadIdx.x) * tiles + tile];
+  if (tile_major) {
+    // up to kFusedScanTiles tiles: no scan launch.  hist holds the raw [seg][tile][bin] counts and every CTA derives the
+    // offset of its (bin, tile) pair itself: keys of smaller bins in all tiles + keys of its bin in earlier tiles
+    // (`tiles` coalesced, independent loads per thread from L2, one block scan).
+    __shared__ int s_warp[9];
+    const uint32_t* h = hist + (int64_t)seg * tiles * kBins + threadIdx.x;
+    uint32_t tot = 0, before = 0;
+#pragma unroll 4
+    for (int t = 0; t < tiles; ++t) {
+      const uint32_t v = h[(int64_t)t * kBins];
+      tot += v;
+      before += t < tile ? v : 0u;
+    }
+    int all;
+    s_base[threadIdx.x] = (uint32_t)block_excl_scan256((int)tot, s_warp, &all) + before;
+  } else {
+    s_base[threadIdx.x] = hist[((int64_t)seg * kBins + threadIdx.x) * tiles + tile];
+  }
   __syncthreads();
 
   const int64_t so = (int64_t)seg * N;
@@ -301,6 +322,8 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
     }
   }
   __syncthreads();
+  // (measured: ordering the tile by digit in shared memory first, so that a warp stores runs of equal digits, made the
+  // pass slower - 0.399 against 0.365 ms for the whole loss at 4 x 34 720 points)
 #pragma unroll
   for (int j = 0; j < kKeysPerThread; ++j) {
     const int idx = wbase + j * 32 + lane;
@@ -496,14 +519,19 @@ extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, co
       const int tiles = (int)ceil_div(N, kSortTile);
       const dim3 sgrid((unsigned)tiles, kC);
       int cur = 0;
+      // beyond kFusedScanTiles the per-CTA prefix reads would grow quadratically (TDSSF_CELS_SCAN=separate: tests)
+      const char* scan_mode = getenv("TDSSF_CELS_SCAN");
+      const bool fused_scan = tiles <= kFusedScanTiles && !(scan_mode && scan_mode[0] == 's');
       for (int pass = 0; pass < kPasses; ++pass) {
         const int shift = pass * kRadixBits;
-        sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, shift, tiles, ws.class_count, ws.hist);
+        sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, shift, tiles, ws.class_count, ws.hist, fused_scan);
         TDSSF_LAUNCH_CHECK();
-        sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count);
-        TDSSF_LAUNCH_CHECK();
+        if (!fused_scan) {
+          sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count);
+          TDSSF_LAUNCH_CHECK();
+        }
         sort_scatter_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1],
-                                                           N, shift, tiles, ws.class_count, ws.hist);
+                                                           N, shift, tiles, ws.class_count, ws.hist, fused_scan);
         TDSSF_LAUNCH_CHECK();
         cur ^= 1;
       }

@@ -335,6 +335,28 @@ def test_cels_vs_oracle_and_sort_properties(ops):
     assert np.abs(x.grad.cpu().numpy() - grad_o).max() <= 3e-5 * np.abs(grad_o).max()
 
 
+def test_cels_scan_paths_agree(ops, monkeypatch):
+    """The radix sort derives its scatter offsets inside the scatter kernel up to 256 tiles per class and with a
+    separate scan launch beyond; both paths must give the same bits (loss, class ids, gradient)."""
+    gen = torch.Generator().manual_seed(33)
+    n = 30_000
+    logits = (torch.randn(2, n, 16, generator=gen) * 2).cuda()
+    labels = synth.make_labels(2, n, gen).cuda()
+    w = torch.tensor(synth.CLASS_WEIGHTS).cuda()
+
+    def run():
+        x = logits.clone().requires_grad_(True)
+        out = ops.cels(x, labels, None, w, 1.0, 0)
+        out[0].backward()
+        return [t.detach().clone() for t in out] + [x.grad.clone()]
+
+    a = run()
+    monkeypatch.setenv("TDSSF_CELS_SCAN", "separate")
+    b = run()
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
 def test_cels_empty_selection(ops):
     from utils.losses import CELSLoss
     crit = CELSLoss(weight=torch.ones(16).cuda())
