@@ -404,3 +404,69 @@ def test_full_size_config2_properties(ops):
     feat2 = ops.gather_mean(d["tokens"] * 2, out["rec"])
     assert torch.equal(feat2, feat * 2)
     assert float(feat[torch.from_numpy(count == 0).cuda()].abs().max()) == 0.0
+
+
+# ---------------------------------------------------------------------------------------------- f3
+def test_evaluation_loop_dropin(ops, capsys):
+    """utils.test.test_model (device-resident confusion matrix and counters) returns exactly what the reference's loop
+    structure returns (per-batch predictions appended on the host, utils/test.py:64-87, then utils.evaluation.evaluate)."""
+    from utils import test as eval_loop
+    from utils.evaluation import evaluate
+    from utils.fusion_model import FeatureFusionModel
+    from utils.losses import CELSLoss
+    n_batches, B, V = 3, 2, 3000
+    sweeps = [synth.make_sweeps(B, V, "dinov2", seed=50 + i) for i in range(n_batches)]
+
+    class ImageEncoder:   # stands in for DINO: the "image" carries the index of its pre-computed token map
+        patch_size, resize_height, resize_width = sweeps[0].encoder.patch_size, sweeps[0].encoder.resize_height, sweeps[0].encoder.resize_width
+
+        def __call__(self, images):
+            out = []
+            for img in images:
+                i, b, v = (int(x) for x in img.flatten()[:3])
+                out.append(sweeps[i].tokens[b, v].cuda())
+            return {"patch_features": torch.stack(out), "global_features": None}
+
+    class Pcd(torch.nn.Module):
+        def forward(self, pts):
+            self.feat = torch.cat([pts, pts.flip(-1)] * 8, -1)[..., :64].contiguous()
+            return self.feat, pts, None, None
+
+        def devoxelize(self, s):
+            return s, None
+
+    def batch(i):
+        sw = sweeps[i]
+        images = torch.zeros(B, 6, 3, 1, 1)
+        for b in range(B):
+            for v in range(6):
+                images[b, v, :, 0, 0] = torch.tensor([i, b, v], dtype=torch.float32)
+        return images, sw.image_sizes, sw.points, sw.labels, sw.mask, sw.K, sw.Rt
+
+    loaders = {"test": [batch(i) for i in range(n_batches)]}
+    enc, pcd = ImageEncoder(), Pcd()
+    model = FeatureFusionModel(enc, pcd, device="cuda").cuda()
+    model.load_state_dict(synth.make_mlp_weights(50), strict=True)
+    crit = CELSLoss(weight=torch.tensor(synth.CLASS_WEIGHTS).cuda())
+    got = eval_loop.test_model(loaders, enc, pcd, model, crit, "cuda")
+    assert "EVALUATION METRICS" in capsys.readouterr().out
+
+    # the reference's loop structure, with the same modules
+    model.eval()
+    tot_loss, correct, points, preds_all, gt_all = 0.0, 0, 0, [], []
+    with torch.no_grad():
+        for images, sizes, pts, labels, mask, K, Rt in loaders["test"]:
+            tokens = torch.stack([enc(images[:, v])["patch_features"] for v in range(6)], dim=1)
+            feat, raw, _, _ = pcd(pts.cuda())
+            out = model(tokens, feat, raw, None, sizes.cuda(), K, Rt)
+            total, _, _, preds, gt = crit(out, labels.cuda(), mask=mask.cuda())
+            tot_loss += total.item()
+            correct += int((preds == gt).sum())
+            points += gt.size(0)
+            preds_all.append(preds.cpu())
+            gt_all.append(gt.cpu())
+    want = evaluate(torch.cat(preds_all), torch.cat(gt_all), 16, tot_loss, float(correct), points, n_batches)
+    assert set(got) == set(want)
+    assert got["overall_acc"] == want["overall_acc"]           # integer counters: exact
+    for k in want:   # fp32 means of the same integer matrix, reduced on the device here and on the host there
+        assert np.allclose(np.asarray(got[k], dtype=np.float64), np.asarray(want[k], dtype=np.float64), rtol=1e-6, atol=1e-9), k
