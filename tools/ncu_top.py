@@ -8,6 +8,7 @@ want = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'l1tex__m_xbar2l1tex_read_bytes.sum', 'l1tex__m_l1tex2xbar_write_bytes.sum', 'l1tex__t_requests_pipe_lsu_mem_local_op_st.sum',
         'smsp__issue_active.avg.pct_of_peak_sustained_active', 'sm__cycles_elapsed.max', 'dram__throughput.avg.pct_of_peak_sustained_elapsed',
         'l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed', 'l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed']
+want += [h for h in hdr if ('bank_conflict' in h or 'data_pipe_lsu_wavefronts_mem_shared' in h or 'l1tex__data_pipe_lsu_wavefronts' in h) and h not in want]
 want += [h for h in hdr if 'pcsamp_warps_issue_stalled' in h and 'not_issued' not in h]
 for w in want:
     if w in hdr:
