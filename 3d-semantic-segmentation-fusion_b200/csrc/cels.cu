@@ -266,16 +266,36 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   __shared__ uint32_t s_base[kBins];          // global offset of (bin, tile)
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < kWarps * kBins; i += kSortThreads) (&s_cnt[0][0])[i] = 0;
+  // warp w owns 256 consecutive keys of the tile, processed as 8 rounds of 32 consecutive keys so
+  // that (round, lane) order == key order  => the ranking below is stable.  All 16 loads of the thread are issued
+  // before anything waits (one round trip to L2 instead of eight), and they overlap the offset computation below.
+  const int64_t so = (int64_t)seg * N;
+  const int wbase = tile * kSortTile + w * (32 * kKeysPerThread);
+  uint32_t key[kKeysPerThread], val[kKeysPerThread], rank[kKeysPerThread];
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int idx = wbase + j * 32 + lane;
+    const bool in = idx < N;
+    key[j] = in ? __ldg(keys_in + so + idx) : 0xffffffffu;
+    val[j] = in ? __ldg(vals_in + so + idx) : 0u;
+  }
   if (tile_major) {
     // up to kFusedScanTiles tiles: no scan launch.  hist holds the raw [seg][tile][bin] counts and every CTA derives the
     // offset of its (bin, tile) pair itself: keys of smaller bins in all tiles + keys of its bin in earlier tiles
-    // (`tiles` coalesced, independent loads per thread from L2, one block scan).
+    // (`tiles` coalesced, independent loads per thread from L2, 16 in flight at a time, one block scan).
     __shared__ int s_warp[9];
     const uint32_t* h = hist + (int64_t)seg * tiles * kBins + threadIdx.x;
     uint32_t tot = 0, before = 0;
-#pragma unroll 4
-    for (int t = 0; t < tiles; ++t) {
-      const uint32_t v = h[(int64_t)t * kBins];
+    int t = 0;
+    for (; t + 16 <= tiles; t += 16) {
+      uint32_t v[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) v[u] = __ldg(h + (int64_t)(t + u) * kBins);
+#pragma unroll
+      for (int u = 0; u < 16; ++u) { tot += v[u]; before += (t + u) < tile ? v[u] : 0u; }
+    }
+    for (; t < tiles; ++t) {
+      const uint32_t v = __ldg(h + (int64_t)t * kBins);
       tot += v;
       before += t < tile ? v : 0u;
     }
@@ -286,17 +306,9 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   }
   __syncthreads();
 
-  const int64_t so = (int64_t)seg * N;
-  // warp w owns 256 consecutive keys of the tile, processed as 8 rounds of 32 consecutive keys so
-  // that (round, lane) order == key order  => the ranking below is stable
-  const int wbase = tile * kSortTile + w * (32 * kKeysPerThread);
-  uint32_t key[kKeysPerThread], val[kKeysPerThread], rank[kKeysPerThread];
 #pragma unroll
   for (int j = 0; j < kKeysPerThread; ++j) {
-    const int idx = wbase + j * 32 + lane;
-    const bool in = idx < N;
-    key[j] = in ? keys_in[so + idx] : 0xffffffffu;
-    val[j] = in ? vals_in[so + idx] : 0u;
+    const bool in = wbase + j * 32 + lane < N;
     const uint32_t d = (key[j] >> shift) & (kBins - 1);
     const uint32_t act = __ballot_sync(0xffffffffu, in);
     uint32_t r = 0;

@@ -149,6 +149,18 @@ def _weights_struct(params: Sequence[torch.Tensor]) -> _lib.MlpWeights:
     return _lib.MlpWeights(*[t.data_ptr() for t in (W1, b1, W2, b2, W3, b3)])
 
 
+def _flat_zero_grads(params: Sequence[torch.Tensor]) -> list:
+    """The six parameter gradients as views of ONE zero-filled fp32 buffer (one fill launch instead of six; the bias
+    sums are accumulated with atomics, so they start from zero).  Every view starts on a 16-byte boundary."""
+    sizes = [t.numel() for t in params]
+    flat = torch.zeros(sum((n + 3) & ~3 for n in sizes), dtype=torch.float32, device=params[0].device)
+    out, off = [], 0
+    for t, n in zip(params, sizes):
+        out.append(flat[off:off + n].view(t.shape))
+        off += (n + 3) & ~3
+    return out
+
+
 class _MlpF32(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x_pt, x_img, W1, b1, W2, b2, W3, b3):
@@ -175,7 +187,7 @@ class _MlpF32(torch.autograd.Function):
         N = xp.shape[0]
         dev = xp.device
         dl = _f32c(dlogits).reshape(-1, 16)
-        grads = [torch.zeros_like(t) for t in (W1, b1, W2, b2, W3, b3)]
+        grads = _flat_zero_grads((W1, b1, W2, b2, W3, b3))
         dx_pt = torch.empty((N, 64), dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
         ws_bytes = lib.tdssf_mlp_bwd_workspace_bytes(N)
         work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -244,7 +256,7 @@ class _MlpTC(torch.autograd.Function):
         N = xp.shape[0]
         dev = xp.device
         dl = _f32c(dlogits).reshape(-1, 16)
-        grads = [torch.zeros_like(t) for t in (W1, b1, W2, b2, W3, b3)]
+        grads = _flat_zero_grads((W1, b1, W2, b2, W3, b3))
         dx_pt = torch.empty((N, 64), dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
         ws_bytes = lib.tdssf_mlp_bwd_tc_workspace_bytes(N)
         work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -335,7 +347,7 @@ class _FusedTrain(torch.autograd.Function):
         N = xb.shape[0]
         dev = xb.device
         dl = _f32c(dlogits).reshape(-1, 16)
-        grads = [torch.zeros_like(t) for t in (W1, b1, W2, b2, W3, b3)]
+        grads = _flat_zero_grads((W1, b1, W2, b2, W3, b3))
         dx_pt = torch.empty((N, 64), dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
         ws_bytes = lib.tdssf_mlp_bwd_tc_workspace_bytes(N)
         work = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -498,3 +510,58 @@ def confusion(preds: torch.Tensor, labels: torch.Tensor, num_classes: int, out: 
     cm = out if out is not None else torch.zeros((num_classes, num_classes), dtype=torch.int64, device=p.device)
     check(lib.tdssf_confusion(_ptr(p), _ptr(l), p.numel(), num_classes, _ptr(cm), _stream(p)), "tdssf_confusion")
     return cm
+
+
+# ------------------------------------------------------------------------------------------------
+# f4  calibration composition, multi-sweep accumulation
+# ------------------------------------------------------------------------------------------------
+def _f64c(t, device) -> torch.Tensor:
+    return torch.as_tensor(t, dtype=torch.float64).to(device).contiguous()
+
+
+def compose_lidar2cam(lidar_sensor, cam_sensor, lidar_ego=None, cam_ego=None, device="cuda", want_f64=False):
+    """Poses (qw,qx,qy,qz,tx,ty,tz): lidar_sensor (B,7), cam_sensor (B,NC,7) [, lidar_ego (B,7), cam_ego (B,NC,7)] ->
+    lidar2cam (B,NC,4,4) fp32 on the device (the `lidar2cam_extrinsics` of utils/dataloader.py:150,226)."""
+    ls, cs = _f64c(lidar_sensor, device), _f64c(cam_sensor, device)
+    if ls.dim() != 2 or ls.shape[1] != 7 or cs.dim() != 3 or cs.shape[2] != 7 or cs.shape[0] != ls.shape[0]:
+        raise ValueError(f"compose_lidar2cam: expected (B,7) and (B,NC,7) poses, got {tuple(ls.shape)} and {tuple(cs.shape)}")
+    if (lidar_ego is None) != (cam_ego is None):
+        raise ValueError("compose_lidar2cam: lidar_ego and cam_ego go together")
+    le = ce = None
+    if lidar_ego is not None:
+        le, ce = _f64c(lidar_ego, device), _f64c(cam_ego, device)
+        if le.shape != ls.shape or ce.shape != cs.shape:
+            raise ValueError("compose_lidar2cam: ego poses must have the shapes of the sensor poses")
+    _need_cuda(ls)
+    B, NC = cs.shape[0], cs.shape[1]
+    out32 = torch.empty((B, NC, 4, 4), dtype=torch.float32, device=ls.device)
+    out64 = torch.empty((B, NC, 4, 4), dtype=torch.float64, device=ls.device) if want_f64 else None
+    check(lib.tdssf_compose_lidar2cam(_ptr(ls), _ptr(cs), _ptr(le), _ptr(ce), B, NC, _ptr(out32), _ptr(out64), _stream(ls)),
+          "tdssf_compose_lidar2cam")
+    return (out32, out64) if want_f64 else out32
+
+
+def accumulate_sweeps(points, counts, sweep_sensor, sweep_ego, ref_sensor, ref_ego):
+    """points (S,P,4) fp32 CUDA (padded sweeps), counts (S,) valid rows; poses as in compose_lidar2cam ->
+    (cloud (S*P,4) fp32 with the first `total` rows filled in sweep order, total (1,) int32 on the device,
+    T (S,4,4) float64).  No host synchronisation: slice with `cloud[:int(total)]` when the length is needed."""
+    _need_cuda(points)
+    if points.dim() != 3 or points.shape[2] != 4 or points.dtype != torch.float32:
+        raise ValueError(f"accumulate_sweeps: points must be (S,P,4) fp32, got {tuple(points.shape)} {points.dtype}")
+    pts = points.contiguous()
+    S, P = pts.shape[0], pts.shape[1]
+    dev = pts.device
+    cnt = torch.as_tensor(counts, dtype=torch.int32).to(dev).contiguous()
+    if cnt.shape != (S,):
+        raise ValueError("accumulate_sweeps: counts must have one entry per sweep")
+    ss, se = _f64c(sweep_sensor, dev), _f64c(sweep_ego, dev)
+    rs, re = _f64c(ref_sensor, dev).reshape(-1), _f64c(ref_ego, dev).reshape(-1)
+    if ss.shape != (S, 7) or se.shape != (S, 7) or rs.shape != (7,) or re.shape != (7,):
+        raise ValueError("accumulate_sweeps: poses must be (S,7), (S,7), (7,), (7,)")
+    T = torch.empty((S, 4, 4), dtype=torch.float64, device=dev)
+    check(lib.tdssf_compose_sweep2ref(_ptr(ss), _ptr(se), _ptr(rs), _ptr(re), S, _ptr(T), _stream(pts)), "tdssf_compose_sweep2ref")
+    cloud = torch.empty((S * P, 4), dtype=torch.float32, device=dev)
+    total = torch.zeros(1, dtype=torch.int32, device=dev)
+    check(lib.tdssf_accumulate_sweeps(_ptr(pts), 4 * P, _ptr(cnt), _ptr(T), S, P, _ptr(cloud), _ptr(total), _stream(pts)),
+          "tdssf_accumulate_sweeps")
+    return cloud, total, T

@@ -262,6 +262,30 @@ TDSSF_API int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, con
 TDSSF_API int tdssf_confusion(const int64_t* preds, const int64_t* labels, int64_t n, int C, int64_t* cm,
                     void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * f4  calibration composition and multi-sweep accumulation (input preparation upstream of a1)
+ * replaces  the numpy block of CustomNuScenesDataset.__getitem__   utils/dataloader.py:123-152
+ *           (lidar2cam = inv(T_cam->ego) @ T_lidar->ego in float64, cast to fp32 at utils/dataloader.py:226)
+ * A pose is 7 doubles: quaternion (w,x,y,z) + translation (x,y,z) — a nuScenes calibrated_sensor / ego_pose record.
+ * lidar_sensor [B,7], cam_sensor [B,NC,7].  lidar_ego [B,7] and cam_ego [B,NC,7] are optional (both or neither):
+ * without them the result is the reference's two-stage product; with them the full chain
+ * lidar -> ego(t_lidar) -> global -> ego(t_cam) -> camera (the records the reference fetches and ignores).
+ * Rt_f32 [B,NC,16] row-major is the `Rt` input of tdssf_project / tdssf_fusion_fwd; Rt_f64 optional. */
+TDSSF_API int tdssf_compose_lidar2cam(const double* lidar_sensor, const double* cam_sensor, const double* lidar_ego,
+                                      const double* cam_ego, int B, int NC, float* Rt_f32, double* Rt_f64, void* stream);
+
+/* Multi-sweep cloud (BASELINE configs[3]); the reference loads one sweep (utils/dataloader.py:63-77), the accumulation
+ * follows nuscenes-devkit LidarPointCloud.from_file_multisweep (dependency pinned in the reference's environment.yml,
+ * source not vendored): T[s] = inv(ref_sensor) . inv(ref_ego) . sweep_ego[s] . sweep_sensor[s], float64.
+ * sweep_sensor, sweep_ego [S,7]; ref_sensor, ref_ego [7]; T_f64 [S,16].  S <= 64. */
+TDSSF_API int tdssf_compose_sweep2ref(const double* sweep_sensor, const double* sweep_ego, const double* ref_sensor,
+                                      const double* ref_ego, int S, double* T_f64, void* stream);
+/* pts [S][P] rows of (x,y,z,intensity) fp32, `sweep_stride_floats` apart; counts [S] int32 (device) valid rows per sweep;
+ * out: the transformed rows packed in sweep order (capacity S*P rows); out_total (device, optional) = sum of counts.
+ * xyz are transformed in float64 and stored as fp32, intensity is copied. */
+TDSSF_API int tdssf_accumulate_sweeps(const float* pts, int64_t sweep_stride_floats, const int32_t* counts, const double* T_f64,
+                                      int S, int P, float* out, int32_t* out_total, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

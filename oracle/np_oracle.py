@@ -466,3 +466,62 @@ def voxelize(points, voxel_size, knn="brute"):
     raw = np.hstack([centres, inten])                                                                   # :103
     coords = np.floor(centres / voxel_size).astype(np.int32)                                            # :108-110
     return raw.astype(F32), coords, vid, mingap                                                         # :113-114
+
+
+# ------------------------------------------------------------------------------------------------
+# f4  calibration composition                                     utils/dataloader.py:123-152
+#     multi-sweep accumulation: nuscenes-devkit LidarPointCloud.from_file_multisweep (dependency of the reference,
+#     environment.yml; source not under the reference tree -> that part is a restatement, parity unpinned)
+# ------------------------------------------------------------------------------------------------
+def pose_matrix(pose):
+    """pose = (qw,qx,qy,qz,tx,ty,tz) float64 -> 4x4.  utils/dataloader.py:127-131,139-143:
+    `T = eye(4); T[:3,:3] = Quaternion(rotation).rotation_matrix; T[:3,3] = translation`.  pyquaternion normalises the
+    quaternion and returns the 3x3 block of Q(q) @ Qbar(q)^T, i.e. the w²+x²−y²−z² form used here."""
+    w, x, y, z = (float(v) for v in pose[:4])
+    n = np.sqrt(w * w + x * x + y * y + z * z)
+    if n > 0:
+        w, x, y, z = w / n, x / n, y / n, z / n
+    T = np.eye(4)
+    T[:3, :3] = [[w * w + x * x - y * y - z * z, 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                 [2 * (x * y + w * z), w * w - x * x + y * y - z * z, 2 * (y * z - w * x)],
+                 [2 * (x * z - w * y), 2 * (y * z + w * x), w * w - x * x - y * y + z * z]]
+    T[:3, 3] = pose[4:7]
+    return T
+
+
+def compose_lidar2cam(lidar_sensor, cam_sensor, lidar_ego=None, cam_ego=None):
+    """lidar_sensor (B,7), cam_sensor (B,NC,7) [, lidar_ego (B,7), cam_ego (B,NC,7)] -> (B,NC,4,4) float64.
+    Without ego poses: utils/dataloader.py:146-149 verbatim, `np.linalg.inv(T_cam_ego) @ T_lidar_ego` (the reference fetches
+    pose_record_lidar / pose_record at :125,138 and never uses them).  With them: the four-stage chain
+    inv(T_cam_ego) @ inv(T_egocam_global) @ T_egolidar_global @ T_lidar_ego."""
+    B, NC = cam_sensor.shape[:2]
+    out = np.zeros((B, NC, 4, 4))
+    for b in range(B):
+        T_lidar_ego = pose_matrix(lidar_sensor[b])
+        for c in range(NC):
+            T = T_lidar_ego
+            if lidar_ego is not None:
+                T = np.linalg.inv(pose_matrix(cam_ego[b, c])) @ (pose_matrix(lidar_ego[b]) @ T)
+            out[b, c] = np.linalg.inv(pose_matrix(cam_sensor[b, c])) @ T
+    return out
+
+
+def compose_sweep2ref(sweep_sensor, sweep_ego, ref_sensor, ref_ego):
+    """(S,7),(S,7),(7,),(7,) -> (S,4,4) float64: ref_from_car @ car_from_global @ global_from_car @ car_from_current."""
+    ref_from_car = np.linalg.inv(pose_matrix(ref_sensor))
+    car_from_global = np.linalg.inv(pose_matrix(ref_ego))
+    return np.stack([ref_from_car @ car_from_global @ pose_matrix(sweep_ego[s]) @ pose_matrix(sweep_sensor[s])
+                     for s in range(len(sweep_sensor))])
+
+
+def accumulate_sweeps(pts, counts, T):
+    """pts (S,P,4) f32, counts (S,), T (S,4,4) f64 -> (sum counts, 4) f32: xyz of sweep s mapped by T[s] in float64
+    (`T.dot(vstack((xyz, ones)))`), stored as fp32; intensity copied; sweeps concatenated in order."""
+    out = []
+    for s in range(len(counts)):
+        p = pts[s, :counts[s]]
+        h = np.vstack((p[:, :3].T.astype(np.float64), np.ones(len(p))))
+        q = p.copy()
+        q[:, :3] = (T[s] @ h)[:3].T.astype(F32)
+        out.append(q)
+    return np.concatenate(out) if out else np.zeros((0, 4), F32)
