@@ -255,7 +255,10 @@ sort_scan_kernel(uint32_t* __restrict__ hist, int tiles, const int* __restrict__
   }
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+#ifndef TDSSF_SCATTER_MINB
+#define TDSSF_SCATTER_MINB 5  // 48 registers: five CTAs per SM (58 registers and four CTAs without the bound: 6 % slower)
+#endif
+__global__ void __launch_bounds__(kSortThreads, TDSSF_SCATTER_MINB)
 sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int N, int shift,
                     int tiles, const int* __restrict__ class_count, const uint32_t* __restrict__ hist, bool tile_major) {
@@ -306,14 +309,21 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   }
   __syncthreads();
 
+  // The eight match operations of a thread do not depend on the counters, so they are all issued first (their latency
+  // overlaps); out-of-range lanes get a digit no key can have.  rank[j] holds the peer mask until the second loop.
 #pragma unroll
   for (int j = 0; j < kKeysPerThread; ++j) {
     const bool in = wbase + j * 32 + lane < N;
     const uint32_t d = (key[j] >> shift) & (kBins - 1);
-    const uint32_t act = __ballot_sync(0xffffffffu, in);
+    rank[j] = __match_any_sync(0xffffffffu, in ? d : (0x100u | (uint32_t)lane));
+  }
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const bool in = wbase + j * 32 + lane < N;
+    const uint32_t d = (key[j] >> shift) & (kBins - 1);
+    const uint32_t peers = rank[j];
     uint32_t r = 0;
     if (in) {
-      const uint32_t peers = __match_any_sync(act, d);
       const int leader = __ffs(peers) - 1;
       uint32_t old = 0;
       if (lane == leader) { old = s_cnt[w][d]; s_cnt[w][d] = old + __popc(peers); }
