@@ -259,3 +259,21 @@ for vs in (0.1, 0.5):
     emit("f1", f"tdssf_voxelize, voxel {vs} m", ms, N, "points",
          note=f"8 sweeps x 34 720 points in one call (down-sample + 5-NN intensity + coords), {int(n_v.float().mean())} voxels per sweep; "
               f"scikit-learn 5-NN alone (part of the reference's host path) on one sweep: {cpu_ms:.1f} ms = {V / cpu_ms * 1e3:.3g} points/s")
+
+# f4: calibration composition (one launch for 8 sweeps x 6 cameras) and the 10-sweep cloud of configs[3]
+import numpy as np
+rng = np.random.default_rng(0)
+def _poses(*shape):
+    q = rng.normal(size=shape + (4,)); q /= np.linalg.norm(q, axis=-1, keepdims=True)
+    return np.concatenate([q, rng.normal(size=shape + (3,))], -1)
+ls_, cs_, le_, ce_ = (torch.from_numpy(x).to(dev) for x in (_poses(B), _poses(B, 6), _poses(B), _poses(B, 6)))
+ms = timeit(lambda: ops.compose_lidar2cam(ls_, cs_, le_, ce_))
+emit("f4", "tdssf_compose_lidar2cam (four-stage chain, float64)", ms, B * 6, "cameras",
+     note="launch-latency bound: 48 threads; the reference composes these on the host with numpy per sample (utils/dataloader.py:123-152)")
+S10 = 10
+p10 = synth.make_points(S10, V, torch.Generator().manual_seed(9)).to(dev)
+cnt10 = torch.full((S10,), V, dtype=torch.int32, device=dev)
+ss_, se_ = (torch.from_numpy(x).to(dev) for x in (_poses(S10), _poses(S10)))
+ms = timeit(lambda: ops.accumulate_sweeps(p10, cnt10, ss_, se_, ss_[0], se_[0]))
+emit("f4", "tdssf_compose_sweep2ref + tdssf_accumulate_sweeps (10 sweeps x 34 720 points)", ms, S10 * V, "points", bytes_per_unit=32,
+     note="16 B in + 16 B out per point, float64 transform; includes the wrapper's two small allocations and the pose kernel")
