@@ -4,16 +4,19 @@ Only the boundary is in scope: the attribute contract the fusion model reads (`p
 `resize_height`, `resize_width`) and the token layout (B, M, 384), row-major y*grid_w+x.  The DINO
 backbone stays the stock Hugging Face module.  Two differences, both on the hand-off:
 tokens stay on the device instead of a per-image .cpu() (set keep_on_device=False for the
-reference behaviour), and the dinov2 branch defines resize_height/resize_width (224), which the
+reference behaviour) and can be handed over in 16 bits (token_dtype), and the dinov2 branch defines resize_height/resize_width (224), which the
 reference's forward needs but its constructor forgets.
 """
 import torch
 
 
 class ImageFeatureEncoder:
-    def __init__(self, config, device="cuda", keep_on_device=True):
+    def __init__(self, config, device="cuda", keep_on_device=True, token_dtype=None):
         self.device = device
         self.keep_on_device = keep_on_device
+        # token_dtype=torch.bfloat16 / torch.float16 hands the tokens over in 16 bits (SURVEY f2): half the bytes every
+        # point gathers; the fusion kernels accept fp32, fp16 and bf16 tokens.  None keeps what the backbone returns.
+        self.token_dtype = token_dtype
         self.model_name = config['train_params']['image_encoder'].lower()
         print("===========================================================")
         print(f"[INFO] Initializing ImageFeatureEncoder: {self.model_name}")
@@ -50,6 +53,8 @@ class ImageFeatureEncoder:
                 inputs = self.processor(images=img, return_tensors="pt").to(self.device)
                 feats = self.model(**inputs).last_hidden_state.squeeze(0)
                 tokens = feats[1:-4]  # the reference drops CLS and the last four (register) tokens
+                if self.token_dtype is not None:
+                    tokens = tokens.to(self.token_dtype)
                 patch.append(tokens if self.keep_on_device else tokens.cpu())
                 cls.append(feats[0] if self.keep_on_device else feats[0].cpu())
         return {"patch_features": torch.stack(patch), "global_features": torch.stack(cls)}
