@@ -115,6 +115,40 @@ def test_fused_full_size_config2(ops):
     assert torch.equal(fused, again)
 
 
+def test_fused_full_size_config4_accumulated_cloud(ops):
+    """BASELINE configs[3] at full size: ten sweeps (each with its own sensor / ego pose) accumulated into one 350 000-point
+    cloud by tdssf_accumulate_sweeps, hi-res 56 x 100 token maps; fused kernel vs the unfused fp32 kernels on that cloud,
+    and the cloud itself against the oracle's float64 transform."""
+    from oracle import np_oracle as O
+    S, P = 10, 35000
+    sw = synth.make_sweeps(1, S * P, "dinov3_hires", seed=4004)
+    rng = np.random.default_rng(4004)
+    raw = sw.points[0].reshape(S, P, 4)
+    q = rng.normal(size=(S, 4)) * 0.02 + np.array([1.0, 0, 0, 0]); q /= np.linalg.norm(q, axis=1, keepdims=True)
+    ego = np.concatenate([q, np.cumsum(rng.normal(size=(S, 3)) * np.array([0.5, 0.1, 0.01]), 0) + np.array([600.0, 900.0, 0])], 1)
+    sensor = np.tile(np.array([1.0, 0, 0, 0, 0.9, 0.0, 1.8]), (S, 1))
+    cloud, total, T = ops.accumulate_sweeps(raw.cuda(), [P] * S, sensor, ego, sensor[0], ego[0])
+    assert int(total.item()) == S * P
+    ref_cloud = O.accumulate_sweeps(raw.numpy(), [P] * S, O.compose_sweep2ref(sensor, ego, sensor[0], ego[0]))
+    got = cloud.cpu().numpy()
+    def _ord(a):   # fp32 bits -> integers in value order (sign-magnitude to two's complement)
+        i = np.ascontiguousarray(a).view(np.int32).astype(np.int64)
+        return np.where(i < 0, -(i & 0x7fffffff), i)
+    ulp = np.abs(_ord(got[:, :3]) - _ord(ref_cloud[:, :3]))
+    assert np.array_equal(got[:, 3], ref_cloud[:, 3]) and ulp.max() <= 2 and (ulp == 0).mean() >= 0.99
+    w = synth.make_mlp_weights(4004)
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    pts = cloud.reshape(1, S * P, 4)
+    K, Rt, hw = torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda()
+    tok, feat = sw.tokens.cuda(), sw.point_feat.cuda()
+    fused = ops.fusion_fwd(pts, K, Rt, hw, sw.encoder, tok, feat, packed)
+    rec = ops.project(pts, K, Rt, hw, sw.encoder, want_pix=False, want_depth=False, want_valid=False, want_rec=True)["rec"]
+    ref = ops.mlp_f32(feat, ops.gather_mean(tok, rec), *wd)
+    assert _rel(fused.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
+    assert int((rec.view(torch.uint8).reshape(1, S * P, 16)[..., 13] > 0).sum()) > S * P // 4   # a real share of the cloud is seen
+
+
 @pytest.mark.parametrize("same", [6, 3])
 def test_fused_overlapping_cameras_and_edge_points(ops, same):
     """Calibrations in which `same` cameras coincide (points seen by up to six cameras: the general camera mean and the
