@@ -66,12 +66,13 @@ static cublasHandle_t handle_for_current_device() {
   return c.handle[dev];
 }
 
-// row-major C[m,n] (ldc) = alpha * op(A) op(B) + beta * C, A and B bf16 row-major, C fp32
+// row-major C[m,n] (ldc) = alpha * op(A) op(B) + beta * C, A and B bf16 row-major, C fp32 (or bf16: c_bf16), fp32 accumulate
 static cublasStatus_t gemm_rm(cublasHandle_t h, bool ta, bool tb, int m, int n, int k, float alpha, const void* A, int lda,
-                              const void* B, int ldb, float beta, float* C, int ldc) {
+                              const void* B, int ldb, float beta, void* C, int ldc, bool c_bf16 = false) {
   // row-major X is column-major X^T: C^T = op(B)^T op(A)^T
   return cublas().gemm_ex(h, tb ? CUBLAS_OP_T : CUBLAS_OP_N, ta ? CUBLAS_OP_T : CUBLAS_OP_N, n, m, k, &alpha, B, CUDA_R_16BF,
-                          ldb, A, CUDA_R_16BF, lda, &beta, C, CUDA_R_32F, ldc, CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT);
+                          ldb, A, CUDA_R_16BF, lda, &beta, C, c_bf16 ? CUDA_R_16BF : CUDA_R_32F, ldc, CUBLAS_COMPUTE_32F,
+                          CUBLAS_GEMM_DEFAULT);
 }
 
 // ---- element-wise kernels -----------------------------------------------------------------------------------
@@ -100,13 +101,14 @@ __global__ void concat_bf16_kernel(const float* __restrict__ x_pt, const float* 
   }
 }
 
-// out = bf16(G * (h > 0)) (h == nullptr: no mask), db[c] += column sums of the masked fp32 values.
+// out = bf16(G * (h > 0)) (h == nullptr: no mask), db[c] += column sums of the masked values.  G is fp32 (the loss
+// gradient) or bf16 (a data-gradient GEMM that wrote bf16 straight into `out`: in place, half the traffic of an fp32
+// round trip, and the same bits - the mask is 0/1, so rounding before or after it is the same rounding).
 // Block = 256 threads = 32 rows x 8 column groups per pass over a [N, C] matrix, C in {16, 64, 256}: thread (ty, tx)
 // walks rows ty, ty+32, ... of its grid-stride slice and columns 8*tx + 64*j.
-template <int C>
+template <int C, typename GT>
 __global__ void __launch_bounds__(256)
-mask_cvt_colsum_kernel(const float* __restrict__ G, const uint16_t* __restrict__ h, uint16_t* __restrict__ out,
-                       float* __restrict__ db, int64_t N) {
+mask_cvt_colsum_kernel(const GT* G, const uint16_t* __restrict__ h, uint16_t* out, float* __restrict__ db, int64_t N) {
   constexpr int kGroups = C / 8;                      // 8-column groups per row
   constexpr int kTx = kGroups < 8 ? kGroups : 8;      // column groups handled side by side
   constexpr int kTy = 256 / kTx;
@@ -121,8 +123,17 @@ mask_cvt_colsum_kernel(const float* __restrict__ G, const uint16_t* __restrict__
 #pragma unroll
     for (int j = 0; j < kJ; ++j) {
       const int c = (tx + j * kTx) * 8;
-      const float4 a = __ldg(reinterpret_cast<const float4*>(G + r * C + c)), b = __ldg(reinterpret_cast<const float4*>(G + r * C + c) + 1);
-      float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      float v[8];
+      if (sizeof(GT) == 4) {
+        const float4* g4 = reinterpret_cast<const float4*>(G + r * C + c);
+        const float4 a = g4[0], b = g4[1];
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+      } else {
+        const uint4 q = *reinterpret_cast<const uint4*>(G + r * C + c);
+        const uint32_t g[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float((e & 1) ? (g[e >> 1] & 0xffff0000u) : (g[e >> 1] << 16));
+      }
       if (h) {
         const uint4 m = __ldg(reinterpret_cast<const uint4*>(h + r * C + c));
         const uint32_t w[4] = {m.x, m.y, m.z, m.w};
@@ -157,7 +168,6 @@ mask_cvt_colsum_kernel(const float* __restrict__ G, const uint16_t* __restrict__
 
 struct Work {
   uint16_t *X, *dl, *dh2, *dh1, *W1, *W2, *W3;
-  float *G2, *G1;
 };
 static size_t al(size_t b) { return (b + 255) & ~(size_t)255; }
 static size_t carve(int64_t N, char* base, Work* w) {
@@ -165,14 +175,12 @@ static size_t carve(int64_t N, char* base, Work* w) {
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += al(bytes); return p; };
   uint16_t* X = (uint16_t*)take((size_t)N * kK1 * 2);
   uint16_t* dl = (uint16_t*)take((size_t)N * kC * 2);
-  float* G2 = (float*)take((size_t)N * kN2 * 4);
   uint16_t* dh2 = (uint16_t*)take((size_t)N * kN2 * 2);
-  float* G1 = (float*)take((size_t)N * kN1 * 4);
   uint16_t* dh1 = (uint16_t*)take((size_t)N * kN1 * 2);
   uint16_t* W1 = (uint16_t*)take((size_t)kN1 * kK1 * 2);
   uint16_t* W2 = (uint16_t*)take((size_t)kN2 * kN1 * 2);
   uint16_t* W3 = (uint16_t*)take((size_t)kC * kN2 * 2);
-  if (w) *w = Work{X, dl, dh2, dh1, W1, W2, W3, G2, G1};
+  if (w) *w = Work{X, dl, dh2, dh1, W1, W2, W3};
   return off;
 }
 
@@ -223,7 +231,7 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     concat_bf16_kernel<<<blocks, 256, 0, s>>>(x_pt, x_img, reinterpret_cast<uint4*>(w.X), N);
     X = w.X;
   }
-  mask_cvt_colsum_kernel<kC><<<blocks, 256, 0, s>>>(dlogits, nullptr, w.dl, g_host->db3, N);
+  mask_cvt_colsum_kernel<kC, float><<<blocks, 256, 0, s>>>(dlogits, nullptr, w.dl, g_host->db3, N);
   TDSSF_LAUNCH_CHECK();
   const int n = (int)N;
   auto ok = [&](cublasStatus_t st, const char* what) {
@@ -232,10 +240,11 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     return false;
   };
   // data gradients
-  if (!ok(gemm_rm(h, false, false, n, kN2, kC, 1.f, w.dl, kC, w.W3, kN2, 0.f, w.G2, kN2), "dH2")) return TDSSF_ECUDA;
-  mask_cvt_colsum_kernel<kN2><<<blocks, 256, 0, s>>>(w.G2, reinterpret_cast<const uint16_t*>(h2_bf16), w.dh2, g_host->db2, N);
-  if (!ok(gemm_rm(h, false, false, n, kN1, kN2, 1.f, w.dh2, kN2, w.W2, kN1, 0.f, w.G1, kN1), "dH1")) return TDSSF_ECUDA;
-  mask_cvt_colsum_kernel<kN1><<<blocks, 256, 0, s>>>(w.G1, reinterpret_cast<const uint16_t*>(h1_bf16), w.dh1, g_host->db1, N);
+  // (the two hidden-layer data gradients leave cuBLAS as bf16, directly in the buffers the mask kernels finish in place)
+  if (!ok(gemm_rm(h, false, false, n, kN2, kC, 1.f, w.dl, kC, w.W3, kN2, 0.f, w.dh2, kN2, true), "dH2")) return TDSSF_ECUDA;
+  mask_cvt_colsum_kernel<kN2, uint16_t><<<blocks, 256, 0, s>>>(w.dh2, reinterpret_cast<const uint16_t*>(h2_bf16), w.dh2, g_host->db2, N);
+  if (!ok(gemm_rm(h, false, false, n, kN1, kN2, 1.f, w.dh2, kN2, w.W2, kN1, 0.f, w.dh1, kN1, true), "dH1")) return TDSSF_ECUDA;
+  mask_cvt_colsum_kernel<kN1, uint16_t><<<blocks, 256, 0, s>>>(w.dh1, reinterpret_cast<const uint16_t*>(h1_bf16), w.dh1, g_host->db1, N);
   TDSSF_LAUNCH_CHECK();
   if (dx_pt && !ok(gemm_rm(h, false, false, n, kCp, kN1, 1.f, w.dh1, kN1, w.W1, kK1, 0.f, dx_pt, kCp), "dx_pt")) return TDSSF_ECUDA;
   // weight gradients, accumulated into the caller's fp32 buffers
