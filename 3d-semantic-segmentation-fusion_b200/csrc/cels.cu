@@ -3,6 +3,11 @@
 //
 //   1. flag rows (mask & label != ignore), count per 256-row tile, scan tile counts      -> N
 //   2. compact + softmax + weighted CE + argmax; emit 16 class segments of sort keys |fg - p_c|
+//   2b. per class, select what has to be sorted: the foreground rows and the background rows whose error is not below
+//      the smallest foreground error.  Everything behind the last foreground element of the sorted order has
+//      intersection 0, Jaccard index exactly 1 and therefore gradient exactly 0 (lovasz_losses.py:25-29), so it
+//      contributes neither to the loss nor to the gradient and its rank is never needed - bit-identical, and for
+//      confident predictions most of the 15 N background keys drop out.  Order-preserving compaction per class.
 //   3. per-class segmented LSD radix sort, descending value, stable (ties by ascending index, F14):
 //      4 passes of 8 bits over key' = 0x3F800000 - bits(err)   (err in [0,1] => key' in [0, 2^30))
 //   4. per class: integer prefix sums of the sorted foreground flags -> Jaccard gradient -> dot
@@ -29,6 +34,9 @@ struct CelsWs {
   int* tile_offset;     // [n_tiles_rows]
   int* n_valid;         // [1]
   int* class_count;     // [16]  foreground count per class (G_c)
+  uint32_t* fg_keymax;  // [16]  largest sort key (= smallest error) among the foreground rows of the class
+  int* seg_count;       // [16]  keys selected for sorting per class
+  int* sel_tile;        // [16][row tiles of the compact rows] selected keys per tile, then their exclusive prefix
   double* acc;          // [0]=sum w*nll  [1]=sum w  [2..17]=lovasz loss per class
   int* rows;            // [N]   original row of compact row i
   uint8_t* ylab;        // [N]   label-1
@@ -52,6 +60,9 @@ static size_t carve(CelsWs* ws, char* base, int64_t n_rows) {
   p = take(row_tiles * sizeof(int)); if (ws) ws->tile_offset = (int*)p;
   p = take(sizeof(int)); if (ws) ws->n_valid = (int*)p;
   p = take(kC * sizeof(int)); if (ws) ws->class_count = (int*)p;
+  p = take(kC * sizeof(uint32_t)); if (ws) ws->fg_keymax = (uint32_t*)p;
+  p = take(kC * sizeof(int)); if (ws) ws->seg_count = (int*)p;
+  p = take((size_t)kC * row_tiles * sizeof(int)); if (ws) ws->sel_tile = (int*)p;
   p = take(18 * sizeof(double)); if (ws) ws->acc = (double*)p;
   p = take(n_rows * sizeof(int)); if (ws) ws->rows = (int*)p;
   p = take(n_rows); if (ws) ws->ylab = (uint8_t*)p;
@@ -100,6 +111,12 @@ __device__ __forceinline__ bool row_is_valid(const int64_t* labels, const uint8_
   return labels[r] != (int64_t)ignore;
 }
 
+// sort key of |fg - p|: ascending key = descending error; err in [0,1] => key in [0, 0x3F800000]
+__device__ __forceinline__ uint32_t sort_key(bool fg, float p) {
+  const float err = fabsf((fg ? 1.f : 0.f) - p);
+  return kOneBits - min(__float_as_uint(err), kOneBits);
+}
+
 // ---- 1. flags ----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kRowTile)
 cels_count_kernel(const int64_t* __restrict__ labels, const uint8_t* __restrict__ mask, int64_t n_rows,
@@ -134,8 +151,9 @@ cels_compact_kernel(const float* __restrict__ logits, const int64_t* __restrict_
                     int64_t* __restrict__ gt) {
   __shared__ int s_warp[9];
   __shared__ int s_cls[kC];
+  __shared__ uint32_t s_kmax[kC];
   __shared__ double s_red[2][8];
-  if (threadIdx.x < kC) s_cls[threadIdx.x] = 0;
+  if (threadIdx.x < kC) { s_cls[threadIdx.x] = 0; s_kmax[threadIdx.x] = 0u; }
   const int64_t r = (int64_t)blockIdx.x * kRowTile + threadIdx.x;
   const int f = (r < n_rows) && row_is_valid(labels, mask, r, ignore);
   int tot;
@@ -181,13 +199,13 @@ cels_compact_kernel(const float* __restrict__ logits, const int64_t* __restrict_
     float4* pd = reinterpret_cast<float4*>(ws.probs + (int64_t)i * kC);
 #pragma unroll
     for (int q = 0; q < 4; ++q) pd[q] = make_float4(p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
+    if (y_ok) {
+      float py = p[0];
 #pragma unroll
-    for (int c = 0; c < kC; ++c) {
-      const float err = fabsf((c == y ? 1.f : 0.f) - p[c]);
-      ws.keys[0][(int64_t)c * N + i] = kOneBits - min(__float_as_uint(err), kOneBits);
-      ws.vals[0][(int64_t)c * N + i] = (uint32_t)i;
+      for (int c = 1; c < kC; ++c) py = (c == y) ? p[c] : py;
+      atomicAdd(&s_cls[y], 1);
+      atomicMax(&s_kmax[y], sort_key(true, py));
     }
-    if (y_ok) atomicAdd(&s_cls[y], 1);
   }
   // block reduction of the CE partial sums
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -203,21 +221,98 @@ cels_compact_kernel(const float* __restrict__ logits, const int64_t* __restrict_
     for (int i = 0; i < 8; ++i) { a += s_red[0][i]; b += s_red[1][i]; }
     if (b != 0.0 || a != 0.0) { atomicAdd(ws.acc + 0, a); atomicAdd(ws.acc + 1, b); }
   }
-  if (threadIdx.x < kC && s_cls[threadIdx.x]) atomicAdd(ws.class_count + threadIdx.x, s_cls[threadIdx.x]);
+  if (threadIdx.x < kC && s_cls[threadIdx.x]) {
+    atomicAdd(ws.class_count + threadIdx.x, s_cls[threadIdx.x]);
+    atomicMax(ws.fg_keymax + threadIdx.x, s_kmax[threadIdx.x]);
+  }
+}
+
+// ---- 2b. selection of the keys that need a rank ---------------------------------------------------------------------
+// One thread per compact row, 16 ballots per warp.  kEmit == false: selected keys per (class, tile) -> sel_tile;
+// kEmit == true: sel_tile holds the exclusive prefix over tiles, keys/values are written in row order (the stable sort's
+// tie-break is the initial order).
+template <bool kEmit>
+__global__ void __launch_bounds__(kRowTile)
+lovasz_select_kernel(CelsWs ws, int tiles) {
+  __shared__ int s_wc[kRowTile / 32][kC];
+  const int N = *ws.n_valid;
+  const int i = blockIdx.x * kRowTile + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float p[kC];
+  int y = -1;
+  if (i < N) {
+    const float4* ps = reinterpret_cast<const float4*>(ws.probs + (int64_t)i * kC);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 v = ps[q];
+      p[4 * q] = v.x; p[4 * q + 1] = v.y; p[4 * q + 2] = v.z; p[4 * q + 3] = v.w;
+    }
+    y = ws.ylab[i];
+  }
+  uint32_t key[kC], sel = 0;   // bit c of sel: this row's key of class c is sorted
+  int rank[kC];
+#pragma unroll
+  for (int c = 0; c < kC; ++c) {
+    key[c] = i < N ? sort_key(c == y, p[c]) : 0u;
+    const bool inc = i < N && ws.class_count[c] > 0 && (c == y || key[c] <= ws.fg_keymax[c]);
+    const uint32_t b = __ballot_sync(0xffffffffu, inc);
+    sel |= (inc ? 1u : 0u) << c;
+    rank[c] = __popc(b & ((1u << lane) - 1));
+    if (lane == 0) s_wc[w][c] = __popc(b);
+  }
+  __syncthreads();
+  if (!kEmit) {
+    if (threadIdx.x < kC) {
+      int tot = 0;
+#pragma unroll
+      for (int ww = 0; ww < kRowTile / 32; ++ww) tot += s_wc[ww][threadIdx.x];
+      ws.sel_tile[threadIdx.x * tiles + blockIdx.x] = tot;
+    }
+    return;
+  }
+#pragma unroll
+  for (int c = 0; c < kC; ++c) {
+    if ((sel >> c) & 1u) {
+      int before = ws.sel_tile[c * tiles + blockIdx.x];
+      for (int ww = 0; ww < w; ++ww) before += s_wc[ww][c];
+      const int64_t pos = (int64_t)c * N + before + rank[c];
+      ws.keys[0][pos] = key[c];
+      ws.vals[0][pos] = (uint32_t)i;
+    }
+  }
+}
+
+// one CTA per class: exclusive scan of the per-tile selection counts, total -> seg_count
+__global__ void __launch_bounds__(256)
+lovasz_segscan_kernel(CelsWs ws, int tiles) {
+  const int seg = blockIdx.x;
+  __shared__ int s_warp[9];
+  int* t = ws.sel_tile + seg * tiles;
+  int carry = 0;
+  for (int base = 0; base < tiles; base += 256) {
+    const int i = base + threadIdx.x;
+    const int v = i < tiles ? t[i] : 0;
+    int tot;
+    const int e = block_excl_scan256(v, s_warp, &tot);
+    if (i < tiles) t[i] = carry + e;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) ws.seg_count[seg] = carry;
 }
 
 // ---- 3. segmented LSD radix sort ------------------------------------------------------------------
 // grid = (sort_tiles, 16 segments).  hist layout [seg][bin][tile] so that one exclusive scan per
 // segment yields the global offset of every (bin, tile) pair.
 __global__ void __launch_bounds__(kSortThreads)
-sort_hist_kernel(const uint32_t* __restrict__ keys, int N, int shift, int tiles,
+sort_hist_kernel(const uint32_t* __restrict__ keys, int Nstride, const int* __restrict__ seg_count, int shift, int tiles,
                  const int* __restrict__ class_count, uint32_t* __restrict__ hist, bool tile_major) {
   const int seg = blockIdx.y, tile = blockIdx.x;
-  if (class_count[seg] == 0) return;  // absent class: skipped by classes='present'
+  const int N = seg_count[seg];   // keys of this class that are sorted; the grid is sized for all valid rows
+  if (class_count[seg] == 0 || tile * kSortTile >= N) return;  // absent class: skipped by classes='present'
   __shared__ uint32_t s_h[kBins];
   s_h[threadIdx.x] = 0;
   __syncthreads();
-  const uint32_t* k = keys + (int64_t)seg * N;
+  const uint32_t* k = keys + (int64_t)seg * Nstride;
   const int base = tile * kSortTile;
 #pragma unroll
   for (int j = 0; j < kKeysPerThread; ++j) {
@@ -231,19 +326,21 @@ sort_hist_kernel(const uint32_t* __restrict__ keys, int N, int shift, int tiles,
 
 // one CTA per segment: in-place exclusive scan over kBins*tiles counters, 8 per thread per step
 __global__ void __launch_bounds__(256)
-sort_scan_kernel(uint32_t* __restrict__ hist, int tiles, const int* __restrict__ class_count) {
+sort_scan_kernel(uint32_t* __restrict__ hist, int tiles, const int* __restrict__ class_count,
+                 const int* __restrict__ seg_count) {
   const int seg = blockIdx.x;
   if (class_count[seg] == 0) return;
   __shared__ int s_warp[9];
   uint32_t* h = hist + (int64_t)seg * kBins * tiles;
   const int64_t n = (int64_t)kBins * tiles;
+  const int tiles_act = (seg_count[seg] + kSortTile - 1) / kSortTile;  // [bin][tile] layout: later tiles were not written
   int carry = 0;
   for (int64_t base = 0; base < n; base += 2048) {
     const int64_t i0 = base + threadIdx.x * 8;
     uint32_t v[8];
     int sum = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { v[j] = (i0 + j < n) ? h[i0 + j] : 0u; sum += (int)v[j]; }
+    for (int j = 0; j < 8; ++j) { v[j] = (i0 + j < n && (int)((i0 + j) % tiles) < tiles_act) ? h[i0 + j] : 0u; sum += (int)v[j]; }
     int tot;
     int run = carry + block_excl_scan256(sum, s_warp, &tot);
 #pragma unroll
@@ -260,10 +357,13 @@ sort_scan_kernel(uint32_t* __restrict__ hist, int tiles, const int* __restrict__
 #endif
 __global__ void __launch_bounds__(kSortThreads, TDSSF_SCATTER_MINB)
 sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int N, int shift,
-                    int tiles, const int* __restrict__ class_count, const uint32_t* __restrict__ hist, bool tile_major) {
+                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int Nstride,
+                    const int* __restrict__ seg_count, int shift, int tiles, const int* __restrict__ class_count,
+                    const uint32_t* __restrict__ hist, bool tile_major) {
   const int seg = blockIdx.y, tile = blockIdx.x;
-  if (class_count[seg] == 0) return;
+  const int N = seg_count[seg];
+  if (class_count[seg] == 0 || tile * kSortTile >= N) return;
+  const int tiles_act = (N + kSortTile - 1) / kSortTile;  // tiles that hold keys (the only histograms written)
   constexpr int kWarps = kSortThreads / 32;
   __shared__ uint32_t s_cnt[kWarps][kBins];   // per-warp digit counters, then exclusive prefix over warps
   __shared__ uint32_t s_base[kBins];          // global offset of (bin, tile)
@@ -272,7 +372,7 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   // warp w owns 256 consecutive keys of the tile, processed as 8 rounds of 32 consecutive keys so
   // that (round, lane) order == key order  => the ranking below is stable.  All 16 loads of the thread are issued
   // before anything waits (one round trip to L2 instead of eight), and they overlap the offset computation below.
-  const int64_t so = (int64_t)seg * N;
+  const int64_t so = (int64_t)seg * Nstride;
   const int wbase = tile * kSortTile + w * (32 * kKeysPerThread);
   uint32_t key[kKeysPerThread], val[kKeysPerThread], rank[kKeysPerThread];
 #pragma unroll
@@ -290,14 +390,14 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
     const uint32_t* h = hist + (int64_t)seg * tiles * kBins + threadIdx.x;
     uint32_t tot = 0, before = 0;
     int t = 0;
-    for (; t + 16 <= tiles; t += 16) {
+    for (; t + 16 <= tiles_act; t += 16) {
       uint32_t v[16];
 #pragma unroll
       for (int u = 0; u < 16; ++u) v[u] = __ldg(h + (int64_t)(t + u) * kBins);
 #pragma unroll
       for (int u = 0; u < 16; ++u) { tot += v[u]; before += (t + u) < tile ? v[u] : 0u; }
     }
-    for (; t < tiles; ++t) {
+    for (; t < tiles_act; ++t) {
       const uint32_t v = __ldg(h + (int64_t)t * kBins);
       tot += v;
       before += t < tile ? v : 0u;
@@ -360,16 +460,18 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
 
 // ---- 4. Jaccard gradient + dot --------------------------------------------------------------------
 __global__ void __launch_bounds__(kSortThreads)
-lovasz_fgcount_kernel(const uint32_t* __restrict__ vals, const uint8_t* __restrict__ ylab, int N, int tiles,
-                      const int* __restrict__ class_count, int* __restrict__ tile_fg) {
+lovasz_fgcount_kernel(const uint32_t* __restrict__ vals, const uint8_t* __restrict__ ylab, int Nstride,
+                      const int* __restrict__ seg_count, int tiles, const int* __restrict__ class_count,
+                      int* __restrict__ tile_fg) {
   const int seg = blockIdx.y, tile = blockIdx.x;
   if (class_count[seg] == 0) return;
+  const int N = seg_count[seg];   // (tiles behind the selected keys write a zero count: the tile scan reads all of them)
   int c = 0;
   const int base = tile * kSortTile + threadIdx.x * kKeysPerThread;
 #pragma unroll
   for (int j = 0; j < kKeysPerThread; ++j) {
     const int idx = base + j;
-    if (idx < N) c += (ylab[vals[(int64_t)seg * N + idx]] == seg);
+    if (idx < N) c += (ylab[vals[(int64_t)seg * Nstride + idx]] == seg);
   }
   __shared__ int s_warp[9];
   int tot;
@@ -403,12 +505,13 @@ __device__ __forceinline__ float jaccard_at(int G, int k /*0-based position*/, i
 
 __global__ void __launch_bounds__(kSortThreads)
 lovasz_grad_dot_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
-                       const uint8_t* __restrict__ ylab, int N, int tiles,
+                       const uint8_t* __restrict__ ylab, int Nstride, const int* __restrict__ seg_count, int tiles,
                        const int* __restrict__ class_count, const int* __restrict__ tile_fg,
                        float* __restrict__ dprob, double* __restrict__ acc) {
   const int seg = blockIdx.y, tile = blockIdx.x;
   const int G = class_count[seg];
-  if (G == 0) return;
+  const int N = seg_count[seg];
+  if (G == 0 || tile * kSortTile >= N) return;
   __shared__ int s_warp[9];
   __shared__ double s_red[8];
   const int base = tile * kSortTile + threadIdx.x * kKeysPerThread;
@@ -417,7 +520,7 @@ lovasz_grad_dot_kernel(const uint32_t* __restrict__ keys, const uint32_t* __rest
 #pragma unroll
   for (int j = 0; j < kKeysPerThread; ++j) {
     const int idx = base + j;
-    v[j] = idx < N ? vals[(int64_t)seg * N + idx] : 0u;
+    v[j] = idx < N ? vals[(int64_t)seg * Nstride + idx] : 0u;
     fg[j] = idx < N ? (ylab[v[j]] == seg) : 0;
     c += fg[j];
   }
@@ -432,7 +535,7 @@ lovasz_grad_dot_kernel(const uint32_t* __restrict__ keys, const uint32_t* __rest
       cf += fg[j];
       const float jac = jaccard_at(G, idx, cf);
       const float g = idx == 0 ? jac : __fsub_rn(jac, jaccard_at(G, idx - 1, cf_prev));
-      const float err = __uint_as_float(kOneBits - keys[(int64_t)seg * N + idx]);
+      const float err = __uint_as_float(kOneBits - keys[(int64_t)seg * Nstride + idx]);
       dot += (double)err * (double)g;
       // d|fg - p| / dp = -sign(fg - p), sign(0) = 0
       const float sgn = err == 0.f ? 0.f : (fg[j] ? -1.f : 1.f);
@@ -518,6 +621,7 @@ extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, co
   carve(&ws, base, std::max<int64_t>(n_rows, 1));
   TDSSF_CUDA(cudaMemsetAsync(ws.n_valid, 0, sizeof(int), s));
   TDSSF_CUDA(cudaMemsetAsync(ws.class_count, 0, kC * sizeof(int), s));
+  TDSSF_CUDA(cudaMemsetAsync(ws.fg_keymax, 0, kC * sizeof(uint32_t), s));
   TDSSF_CUDA(cudaMemsetAsync(ws.acc, 0, 18 * sizeof(double), s));
   if (dlogits && n_rows) TDSSF_CUDA(cudaMemsetAsync(dlogits, 0, (size_t)n_rows * kC * sizeof(float), s));
   *n_valid_host = 0;
@@ -538,7 +642,17 @@ extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, co
       const int N = n_valid;
       cels_compact_kernel<<<row_tiles, kRowTile, 0, s>>>(logits, labels, mask, n_rows, ignore_index, class_w, ws, preds, gt);
       TDSSF_LAUNCH_CHECK();
-      const int tiles = (int)ceil_div(N, kSortTile);
+      // TDSSF_CELS_SELECT=all (tests): every key of a present class is sorted, as the reference does
+      const char* sel_mode = getenv("TDSSF_CELS_SELECT");
+      if (sel_mode && sel_mode[0] == 'a') TDSSF_CUDA(cudaMemsetAsync(ws.fg_keymax, 0xff, kC * sizeof(uint32_t), s));
+      const int sel_tiles = (int)ceil_div(N, kRowTile);
+      lovasz_select_kernel<false><<<sel_tiles, kRowTile, 0, s>>>(ws, sel_tiles);
+      TDSSF_LAUNCH_CHECK();
+      lovasz_segscan_kernel<<<kC, 256, 0, s>>>(ws, sel_tiles);
+      TDSSF_LAUNCH_CHECK();
+      lovasz_select_kernel<true><<<sel_tiles, kRowTile, 0, s>>>(ws, sel_tiles);
+      TDSSF_LAUNCH_CHECK();
+      const int tiles = (int)ceil_div(N, kSortTile);   // upper bound: the kernels read the selected count per class
       const dim3 sgrid((unsigned)tiles, kC);
       int cur = 0;
       // beyond kFusedScanTiles the per-CTA prefix reads would grow quadratically (TDSSF_CELS_SCAN=separate: tests)
@@ -546,23 +660,23 @@ extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, co
       const bool fused_scan = tiles <= kFusedScanTiles && !(scan_mode && scan_mode[0] == 's');
       for (int pass = 0; pass < kPasses; ++pass) {
         const int shift = pass * kRadixBits;
-        sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, shift, tiles, ws.class_count, ws.hist, fused_scan);
+        sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, ws.seg_count, shift, tiles, ws.class_count, ws.hist, fused_scan);
         TDSSF_LAUNCH_CHECK();
         if (!fused_scan) {
-          sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count);
+          sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count, ws.seg_count);
           TDSSF_LAUNCH_CHECK();
         }
         sort_scatter_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1],
-                                                           N, shift, tiles, ws.class_count, ws.hist, fused_scan);
+                                                           N, ws.seg_count, shift, tiles, ws.class_count, ws.hist, fused_scan);
         TDSSF_LAUNCH_CHECK();
         cur ^= 1;
       }
       TDSSF_CUDA(cudaMemsetAsync(ws.dprob, 0, (size_t)N * kC * sizeof(float), s));
-      lovasz_fgcount_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.vals[cur], ws.ylab, N, tiles, ws.class_count, ws.tile_fg);
+      lovasz_fgcount_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.vals[cur], ws.ylab, N, ws.seg_count, tiles, ws.class_count, ws.tile_fg);
       TDSSF_LAUNCH_CHECK();
       lovasz_tilescan_kernel<<<kC, 256, 0, s>>>(ws.tile_fg, tiles, ws.class_count);
       TDSSF_LAUNCH_CHECK();
-      lovasz_grad_dot_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.ylab, N, tiles, ws.class_count,
+      lovasz_grad_dot_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.ylab, N, ws.seg_count, tiles, ws.class_count,
                                                             ws.tile_fg, ws.dprob, ws.acc);
       TDSSF_LAUNCH_CHECK();
       if (dlogits) {

@@ -357,6 +357,36 @@ def test_cels_scan_paths_agree(ops, monkeypatch):
         assert torch.equal(x, y)
 
 
+@pytest.mark.parametrize("scale", [1.0, 6.0])
+def test_cels_key_selection_is_exact(ops, monkeypatch, scale):
+    """Only the foreground keys and the background keys not below the smallest foreground error are sorted (everything
+    behind the last foreground element has Jaccard gradient exactly 0); sorting all 16 N keys like the reference must give
+    the same bits - loss, class ids and gradient - for flat (scale 1) and confident (scale 6) predictions, with ties."""
+    gen = torch.Generator().manual_seed(35)
+    n = 40_000
+    logits = torch.randn(2, n, 16, generator=gen) * scale
+    labels = synth.make_labels(2, n, gen)
+    logits[0, :n // 2] += 2.0 * scale * torch.nn.functional.one_hot(labels[0, :n // 2].clamp(min=1) - 1, 16)  # partly trained
+    logits[1, ::7] = torch.round(logits[1, ::7])                                                            # ties
+    logits, labels, w = logits.cuda(), labels.cuda(), torch.tensor(synth.CLASS_WEIGHTS).cuda()
+
+    def run():
+        x = logits.clone().requires_grad_(True)
+        out = ops.cels(x, labels, None, w, 1.0, 0)
+        out[0].backward()
+        return [t.detach().clone() for t in out] + [x.grad.clone()]
+
+    a = run()
+    monkeypatch.setenv("TDSSF_CELS_SELECT", "all")
+    b = run()
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    t_o, _, lov_o, _, _, grad_o = O.cels_loss(logits.cpu().numpy(), labels.cpu().numpy(), None, w.cpu().numpy(), 0, 1.0, return_grad=True)
+    assert abs(a[2].item() - lov_o) < 1e-5 * abs(lov_o)
+    # fp32 softmax backward against the float64 oracle (the bits of the two device paths are compared above)
+    assert np.abs(a[5].cpu().numpy() - grad_o).max() <= 1e-3 * np.abs(grad_o).max()
+
+
 def test_cels_empty_selection(ops):
     from utils.losses import CELSLoss
     crit = CELSLoss(weight=torch.ones(16).cuda())
