@@ -58,12 +58,12 @@ static size_t carve(CelsWs* ws, char* base, int64_t n_rows) {
   char* p;
   p = take(row_tiles * sizeof(int)); if (ws) ws->tile_count = (int*)p;
   p = take(row_tiles * sizeof(int)); if (ws) ws->tile_offset = (int*)p;
-  p = take(sizeof(int)); if (ws) ws->n_valid = (int*)p;
-  p = take(kC * sizeof(int)); if (ws) ws->class_count = (int*)p;
+  p = take(sizeof(int)); if (ws) ws->n_valid = (int*)p;              // } zeroed by one memset at the start of a call:
+  p = take(kC * sizeof(int)); if (ws) ws->class_count = (int*)p;     // } keep these five together and in this order
   p = take(kC * sizeof(uint32_t)); if (ws) ws->fg_keymax = (uint32_t*)p;
   p = take(kC * sizeof(int)); if (ws) ws->seg_count = (int*)p;
-  p = take((size_t)kC * row_tiles * sizeof(int)); if (ws) ws->sel_tile = (int*)p;
   p = take(18 * sizeof(double)); if (ws) ws->acc = (double*)p;
+  p = take((size_t)kC * row_tiles * sizeof(int)); if (ws) ws->sel_tile = (int*)p;
   p = take(n_rows * sizeof(int)); if (ws) ws->rows = (int*)p;
   p = take(n_rows); if (ws) ws->ylab = (uint8_t*)p;
   p = take(n_rows * kC * sizeof(float)); if (ws) ws->probs = (float*)p;
@@ -619,10 +619,8 @@ extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, co
   CelsWs ws;
   char* base = reinterpret_cast<char*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   carve(&ws, base, std::max<int64_t>(n_rows, 1));
-  TDSSF_CUDA(cudaMemsetAsync(ws.n_valid, 0, sizeof(int), s));
-  TDSSF_CUDA(cudaMemsetAsync(ws.class_count, 0, kC * sizeof(int), s));
-  TDSSF_CUDA(cudaMemsetAsync(ws.fg_keymax, 0, kC * sizeof(uint32_t), s));
-  TDSSF_CUDA(cudaMemsetAsync(ws.acc, 0, 18 * sizeof(double), s));
+  // n_valid, class_count, fg_keymax, seg_count and acc are carved next to each other: one memset
+  TDSSF_CUDA(cudaMemsetAsync(ws.n_valid, 0, (size_t)(reinterpret_cast<char*>(ws.acc + 18) - reinterpret_cast<char*>(ws.n_valid)), s));
   if (dlogits && n_rows) TDSSF_CUDA(cudaMemsetAsync(dlogits, 0, (size_t)n_rows * kC * sizeof(float), s));
   *n_valid_host = 0;
   if (n_rows > 0) {

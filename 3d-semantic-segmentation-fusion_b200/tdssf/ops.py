@@ -480,7 +480,8 @@ class _Cels(torch.autograd.Function):
         ctx.dlog = dlog
         ctx.in_shape = tuple(logits.shape)
         ctx.mark_non_differentiable(preds, gt)
-        return scal[0].clone(), scal[1].clone(), scal[2].clone(), preds[:n], gt[:n]
+        total, ce, lov, _ = scal.unbind(0)   # `scal` is this call's own buffer: no copies needed
+        return total, ce, lov, preds[:n], gt[:n]
 
     @staticmethod
     def backward(ctx, g_total, g_ce, g_lov, _gp, _gg):
