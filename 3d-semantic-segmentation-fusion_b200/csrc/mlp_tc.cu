@@ -13,8 +13,9 @@
 //                the load/store unit every memory instruction of another warp queues for hundreds of cycles.
 //   warps 0-7    epilogue (72 regs): TMEM -> registers -> bias/ReLU -> bf16 -> TMEM (A operand of the next layer), in
 //                16-column chunks with the next TMEM load in flight; last layer -> logits to HBM
-//   warp  8      TMEM allocation, weight load (cp.async.bulk), event-driven MMA issue (leader CTA only)   (64 regs)
-//   warps 9-11   idle after the prologue (keep the warpgroups aligned)
+//   warp  8      TMEM allocation, weight load (cp.async.bulk), layer-1 MMA issue (leader CTA only)       (64 regs)
+//   warp  9      layer-2 / layer-3 MMA issue as soon as the epilogue has written H1 / H2 (leader CTA only)
+//   warps 10-11  idle after the prologue (keep the warpgroups aligned; their registers go to the producers)
 //   warps 12-19  producers (136 regs): per 64-channel K slab, gather of the rows' sources (L2/HBM) with
 //                [pointer + immediate] loads, fp32 -> bf16, written in the 128B-swizzled K-major layout the UMMA
 //                descriptor expects.  A thread owns a quarter of four rows; three register sets: the loads of slabs
@@ -23,8 +24,8 @@
 // TMEM (512 columns) holds two 256-column tile buffers; inside a buffer the layer-1 accumulator is overwritten in
 // place by its own bf16 activation (H1), and the layer-2/3 accumulators and H2 reuse columns already consumed:
 //   [0,256) acc1   ->   [0,64) H1 lo | [64,128) acc2 | [128,192) H1 hi | [192,224) H2 | [224,256) acc3
-// The MMA thread issues layer 1 of tile t+1 slab by slab as the producers deliver, and services tile t (layer 2 when
-// H1 is written, layer 3 when H2 is written) in between, so the small layers never wait behind a slow producer.
+// One thread issues layer 1 of tile t+1 slab by slab as the producers deliver; a second thread issues the small layers of
+// tile t (layer 2 when H1 is written, layer 3 when H2 is written), so neither waits behind the other's barriers.
 #include <algorithm>
 #include <type_traits>
 #include "project.cuh"

@@ -65,6 +65,17 @@ def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
         return 0
     _, w = world()
     dev = params[0].device
+    shared = _shared_flat_grad(params)
+    if shared is not None:
+        # the bf16 backward hands out the six gradients as views of one buffer (tdssf.ops._flat_zero_grads) and autograd
+        # keeps them: the bucket already exists, reduce it in place (one collective, no gather / scatter copies)
+        if w > 1:
+            if dist.get_backend() == "nccl":
+                dist.all_reduce(shared, op=dist.ReduceOp.AVG)
+            else:
+                dist.all_reduce(shared, op=dist.ReduceOp.SUM)
+                shared.div_(w)
+        return shared.numel()
     flat = torch.zeros(sum(p.numel() for p in params), dtype=torch.float32, device=dev)
     off = 0
     for p in params:
@@ -83,6 +94,23 @@ def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
             p.grad.copy_(g)
         off += p.numel()
     return flat.numel()
+
+
+def _shared_flat_grad(params):
+    """The gradients of `params` as ONE 1-D fp32 tensor if they are back-to-back views of a single storage, else None."""
+    g0 = params[0].grad
+    if g0 is None or g0.dtype != torch.float32:
+        return None
+    base = g0.untyped_storage().data_ptr()
+    ptr = g0.data_ptr()
+    total = 0
+    for p in params:
+        g = p.grad
+        if (g is None or g.dtype != torch.float32 or not g.is_contiguous() or g.untyped_storage().data_ptr() != base
+                or g.data_ptr() != ptr + 4 * total):
+            return None
+        total += g.numel()
+    return torch.empty(0, dtype=torch.float32, device=g0.device).set_(g0.untyped_storage(), g0.storage_offset(), (total,))
 
 
 def max_over_ranks(value: float, device=None) -> float:

@@ -121,3 +121,28 @@ def _missing_grad_worker(rank, world_size):
 
 def test_rank_without_grads_contributes_zeros():
     _run(_missing_grad_worker, 2)
+
+
+def _shared_flat_worker(rank, world_size):
+    """Gradients that are back-to-back views of one buffer (what the bf16 backward hands to autograd) are reduced in place."""
+    mlp = torch.nn.Sequential(torch.nn.Linear(8, 4), torch.nn.ReLU(), torch.nn.Linear(4, 4))
+    params = list(mlp.parameters())
+    flat = torch.randn(sum(p.numel() for p in params), generator=torch.Generator().manual_seed(100 + rank))
+    mine = flat.clone()
+    off = 0
+    for p in params:
+        p.grad = flat[off:off + p.numel()].view_as(p)
+        off += p.numel()
+    assert parallel._shared_flat_grad(params) is not None
+    n = parallel.allreduce_mean_grads(params)
+    assert n == flat.numel()
+    other = torch.randn(flat.numel(), generator=torch.Generator().manual_seed(100 + 1 - rank))
+    torch.testing.assert_close(flat, (mine + other) / 2)          # reduced in place: the views see the mean
+    assert params[0].grad.untyped_storage().data_ptr() == flat.untyped_storage().data_ptr()
+    # a gap between the views (or a foreign storage) falls back to the gather / scatter path
+    params[1].grad = params[1].grad.clone()
+    assert parallel._shared_flat_grad(params) is None
+
+
+def test_shared_flat_grad_bucket_gloo_ws2():
+    _run(_shared_flat_worker, 2)

@@ -88,6 +88,7 @@ if rank == 0:
     print(json.dumps({"row": "config3", "n_gpus": world, "sweeps_per_gpu": PER_RANK, "points_per_sweep": V,
                       "ms_per_step": round(ms, 4), "points_per_s": round(world * PER_RANK * V / ms * 1e3),
                       "allreduce": "one flat fp32 bucket of the 132 432 MLP gradients, mean",
+                   "bucket_in_place": parallel._shared_flat_grad([p for p in model.mlp.parameters()]) is not None,
                       "grad_vs_mean_of_shards_rel_err": err, "loss_rank0": float(loss)}), flush=True)
     assert err < 1e-5, err
 
