@@ -36,4 +36,4 @@ pr = cProfile.Profile(); pr.enable()
 for _ in range(100): step()
 torch.cuda.synchronize()
 pr.disable()
-st = pstats.Stats(pr); st.sort_stats("tottime").print_stats(28)
+st = pstats.Stats(pr); st.strip_dirs(); st.sort_stats("cumtime").print_stats(45)
