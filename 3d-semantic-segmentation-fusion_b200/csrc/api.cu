@@ -1,4 +1,5 @@
 // Library-level entry points: version, error string, device check.
+#include <cstdlib>
 #include <stdarg.h>
 #include <string.h>
 #include "common.cuh"
@@ -23,6 +24,12 @@ int num_sms() {
       cached = n;
     else
       cached = 148;
+    // experiment hook: TDSSF_SMS=<n> sizes every persistent grid (and the workspaces derived from it) for fewer SMs, to
+    // tell a per-SM limit from a chip-wide one (profiles/r1_experiments_v10.md)
+    if (const char* e = getenv("TDSSF_SMS")) {
+      const int v = atoi(e);
+      if (v >= 2 && v < cached) cached = v & ~1;
+    }
   }
   return cached;
 }
