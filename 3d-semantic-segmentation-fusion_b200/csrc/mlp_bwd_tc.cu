@@ -81,11 +81,16 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// dst[i] = bf16(src[i]), 8 elements per thread (n % 8 == 0)
-__global__ void cvt_bf16_kernel(const float* __restrict__ src, uint4* __restrict__ dst, int64_t n8) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * i), b = __ldg(reinterpret_cast<const float4*>(src) + 2 * i + 1);
-    dst[i] = make_uint4(pack2(a.x, a.y), pack2(a.z, a.w), pack2(b.x, b.y), pack2(b.z, b.w));
+// dst[i] = bf16(src[i]), 8 elements per thread (every count is a multiple of 8);
+// the three weight matrices in one launch (the training step is bound by the host's launches, not by this kernel)
+__global__ void cvt3_bf16_kernel(const float* __restrict__ s0, uint4* __restrict__ d0, int64_t n0, const float* __restrict__ s1,
+                                 uint4* __restrict__ d1, int64_t n1, const float* __restrict__ s2, uint4* __restrict__ d2, int64_t n2) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1 + n2; i += (int64_t)gridDim.x * blockDim.x) {
+    const float* src = i < n0 ? s0 : i < n0 + n1 ? s1 : s2;
+    uint4* dst = i < n0 ? d0 : i < n0 + n1 ? d1 : d2;
+    const int64_t k = i < n0 ? i : i < n0 + n1 ? i - n0 : i - n0 - n1;
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * k), b = __ldg(reinterpret_cast<const float4*>(src) + 2 * k + 1);
+    dst[k] = make_uint4(pack2(a.x, a.y), pack2(a.z, a.w), pack2(b.x, b.y), pack2(b.z, b.w));
   }
 }
 
@@ -223,9 +228,9 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
   carve(N, reinterpret_cast<char*>(workspace), &w);
   const unsigned blocks = (unsigned)num_sms() * 8;
   // operands in bf16
-  cvt_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W1, reinterpret_cast<uint4*>(w.W1), (int64_t)kN1 * kK1 / 8);
-  cvt_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W2, reinterpret_cast<uint4*>(w.W2), (int64_t)kN2 * kN1 / 8);
-  cvt_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W3, reinterpret_cast<uint4*>(w.W3), (int64_t)kC * kN2 / 8);
+  cvt3_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W1, reinterpret_cast<uint4*>(w.W1), (int64_t)kN1 * kK1 / 8,
+                                          w_host->W2, reinterpret_cast<uint4*>(w.W2), (int64_t)kN2 * kN1 / 8,
+                                          w_host->W3, reinterpret_cast<uint4*>(w.W3), (int64_t)kC * kN2 / 8);
   const void* X = x_bf16;
   if (!X) {
     concat_bf16_kernel<<<blocks, 256, 0, s>>>(x_pt, x_img, reinterpret_cast<uint4*>(w.X), N);
