@@ -1,4 +1,5 @@
 // Library-level entry points: version, error string, device check.
+#include <atomic>
 #include <cstdlib>
 #include <stdarg.h>
 #include <string.h>
@@ -15,23 +16,29 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+int current_device() {
+  int dev = 0;
+  return cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < kMaxDevices ? dev : 0;
+}
+
+// per device: one process may drive several GPUs (one library instance, kernels launched on the current device)
 int num_sms() {
-  static int cached = 0;
-  if (cached == 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-      cached = n;
-    else
-      cached = 148;
-    // experiment hook: TDSSF_SMS=<n> sizes every persistent grid (and the workspaces derived from it) for fewer SMs, to
-    // tell a per-SM limit from a chip-wide one (profiles/r1_experiments_v10.md)
+  static std::atomic<int> cached[kMaxDevices];
+  const int dev = current_device();
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+#ifdef TDSSF_EXPERIMENT
+    // experiment builds only: TDSSF_SMS=<n> sizes every persistent grid (and the workspaces derived from it) for fewer
+    // SMs, to tell a per-SM limit from a chip-wide one (profiles/r1_experiments_v10.md)
     if (const char* e = getenv("TDSSF_SMS")) {
       const int v = atoi(e);
-      if (v >= 2 && v < cached) cached = v & ~1;
+      if (v >= 2 && v < n) n = v & ~1;
     }
+#endif
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached;
+  return n;
 }
 
 }  // namespace tdssf

@@ -570,17 +570,21 @@ __global__ void cels_finalize_kernel(CelsWs ws, float lambda, float* __restrict_
 }
 
 __global__ void __launch_bounds__(256)
-cels_backward_kernel(CelsWs ws, const float* __restrict__ class_w, float lambda, float* __restrict__ dlogits) {
+cels_backward_kernel(CelsWs ws, const float* __restrict__ class_w, float a_ce, float a_lov, const float* __restrict__ coef,
+                     float* __restrict__ dlogits) {
+  // dlogits = a_ce * d ce / d logits + a_lov * d lovasz / d logits; the forward call uses (1, lambda) = d total; `coef`
+  // (device, optional) overrides both with the upstream gradients of a backward pass through ce / lovasz themselves
   const int N = *ws.n_valid;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
+  if (coef) { a_ce = __ldg(coef); a_lov = __ldg(coef + 1); }
   int n_present = 0;
 #pragma unroll
   for (int c = 0; c < kC; ++c) n_present += ws.class_count[c] > 0;
-  const float lscale = n_present > 0 ? lambda / (float)n_present : 0.f;
+  const float lscale = n_present > 0 ? a_lov / (float)n_present : 0.f;
   const float wsum = (float)ws.acc[1];
   const int y = ws.ylab[i];
-  const float wy = y < kC ? __ldg(class_w + y) / wsum : 0.f;
+  const float wy = y < kC ? a_ce * (__ldg(class_w + y) / wsum) : 0.f;
   float p[kC], dp[kC], s = 0.f;
   const float4* ps = reinterpret_cast<const float4*>(ws.probs + (int64_t)i * kC);
   const float4* ds = reinterpret_cast<const float4*>(ws.dprob + (int64_t)i * kC);
@@ -678,12 +682,31 @@ extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, co
                                                             ws.tile_fg, ws.dprob, ws.acc);
       TDSSF_LAUNCH_CHECK();
       if (dlogits) {
-        cels_backward_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, s>>>(ws, class_w, lambda_lovasz, dlogits);
+        cels_backward_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, s>>>(ws, class_w, 1.f, lambda_lovasz, nullptr, dlogits);
         TDSSF_LAUNCH_CHECK();
       }
     }
   }
   cels_finalize_kernel<<<1, 1, 0, s>>>(ws, lambda_lovasz, out_scalars);
+  TDSSF_LAUNCH_CHECK();
+  return TDSSF_OK;
+}
+
+extern "C" int tdssf_cels_backward(const void* workspace, size_t workspace_bytes, int64_t n_rows, int64_t n_valid,
+                                   const float* class_w, const float* coef, float* dlogits, void* stream) {
+  using namespace tdssf;
+  TDSSF_REQUIRE(workspace && class_w && coef && dlogits, "tdssf_cels_backward: NULL pointer");
+  TDSSF_REQUIRE(n_rows >= 0 && n_valid >= 0 && n_valid <= n_rows, "tdssf_cels_backward: bad row counts");
+  TDSSF_REQUIRE(workspace_bytes >= tdssf_cels_workspace_bytes(n_rows), "tdssf_cels_backward: workspace too small");
+  TDSSF_REQUIRE(((uintptr_t)dlogits & 15) == 0, "tdssf_cels_backward: dlogits must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n_rows == 0) return TDSSF_OK;
+  TDSSF_CUDA(cudaMemsetAsync(dlogits, 0, (size_t)n_rows * kC * sizeof(float), s));
+  if (n_valid == 0) return TDSSF_OK;
+  CelsWs ws;
+  char* base = reinterpret_cast<char*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  carve(&ws, base, std::max<int64_t>(n_rows, 1));
+  cels_backward_kernel<<<(unsigned)ceil_div(n_valid, 256), 256, 0, s>>>(ws, class_w, 0.f, 0.f, coef, dlogits);
   TDSSF_LAUNCH_CHECK();
   return TDSSF_OK;
 }

@@ -41,7 +41,9 @@ void set_error(const char* fmt, ...);
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
-int num_sms();
+constexpr int kMaxDevices = 64;
+int current_device();  // index of the current CUDA device (0 when it cannot be read), < kMaxDevices
+int num_sms();         // SM count of the current device (cached per device)
 
 // streaming (read-once) 16-byte load that does not allocate in L1
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {

@@ -76,14 +76,23 @@ __device__ __forceinline__ uint32_t cell_hash(int ix, int iy, int iz, uint32_t m
 }
 __device__ __forceinline__ int cell_of(float x, float inv_cell) { return __float2int_rd(__fmul_rn(x, inv_cell)); }
 
-// one thread per voxel: node = (x, y, z, next voxel of the same bucket), pushed at the head of its bucket's list
+// one thread per voxel: node = (x, y, z, next voxel of the same bucket), pushed at the head of its bucket's list.
+// Rows at exactly (0,0,0) - the zero padding of voxel_raw up to V_max, hundreds to thousands of identical
+// rows - are not linked (they would form one long serial bucket walk for every point near the origin): only the lowest
+// such index can ever win (equal distance, first index wins), so it is kept in first_zero[b] and offered to every
+// query as one extra candidate.
 __global__ void devox_grid_build_kernel(const float* __restrict__ vox, int64_t vox_stride, int V, float inv_cell,
-                                        int* __restrict__ head, uint32_t mask, float4* __restrict__ node) {
+                                        int* __restrict__ head, uint32_t mask, float4* __restrict__ node,
+                                        int* __restrict__ first_zero) {
   const int b = blockIdx.y;
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= V) return;
   const float* q = vox + ((int64_t)b * V + v) * vox_stride;
   const float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+  if (x == 0.f && y == 0.f && z == 0.f) {
+    atomicMin(first_zero + b, v);
+    return;
+  }
   const uint32_t h = cell_hash(cell_of(x, inv_cell), cell_of(y, inv_cell), cell_of(z, inv_cell), mask);
   const int old = atomicExch(head + (int64_t)b * (mask + 1) + h, v);
   node[(int64_t)b * V + v] = make_float4(x, y, z, __int_as_float(old));
@@ -95,8 +104,10 @@ constexpr int kQueryThreads = 256;
 __global__ void __launch_bounds__(kQueryThreads)
 devox_grid_query_kernel(const float* __restrict__ pts, int64_t pts_stride, int P, int V, float inv_cell, float accept_d2,
                         const int* __restrict__ head, uint32_t mask, const float4* __restrict__ node,
-                        int64_t* __restrict__ idx, int* __restrict__ todo, int* __restrict__ n_todo) {
+                        const int* __restrict__ first_zero, int64_t* __restrict__ idx, int* __restrict__ todo,
+                        int* __restrict__ n_todo) {
   const int b = blockIdx.y, lane = threadIdx.x & 31;
+  const int vz = __ldg(first_zero + b);  // lowest row at the origin, or >= V when there is none
   const int* hb = head + (int64_t)b * (mask + 1);
   const float4* nb = node + (int64_t)b * V;
   const int dx = lane % 3 - 1, dy = (lane / 3) % 3 - 1, dz = lane / 9 - 1;  // lanes 27..31: no cell
@@ -113,6 +124,9 @@ devox_grid_query_kernel(const float* __restrict__ pts, int64_t pts_stride, int P
         if (d < best || (d == best && v < besti)) { best = d; besti = v; }
         v = __float_as_int(c.w);
       }
+    } else if (lane == 27 && vz < V) {  // the origin rows' representative
+      best = dist2_rn(px, py, pz, 0.f, 0.f, 0.f);
+      besti = vz;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -216,11 +230,11 @@ static uint32_t devox_table_size(int V) {
   while (t < 2u * (uint32_t)V) t <<= 1;
   return t;
 }
-// workspace: [B][T] bucket heads, [B][V] nodes (16 B), [B*P] unresolved points, counter
+// workspace: [B][T] bucket heads, [B][V] nodes (16 B), [B*P] unresolved points, counter, [B] first origin row
 static size_t devox_ws_bytes(int B, int P, int V) {
   const size_t T = devox_table_size(V);
   return (((size_t)B * T * 4 + 255) & ~(size_t)255) + (((size_t)B * V * 16 + 255) & ~(size_t)255) +
-         (((size_t)B * P * 4 + 255) & ~(size_t)255) + 256;
+         (((size_t)B * P * 4 + 255) & ~(size_t)255) + 256 + (((size_t)B * 4 + 255) & ~(size_t)255);
 }
 
 extern "C" size_t tdssf_devox_nn_workspace_bytes(int B, int P, int V) {
@@ -257,16 +271,19 @@ extern "C" int tdssf_devox_nn(const float* pts, int64_t pts_stride, const float*
   int* todo = reinterpret_cast<int*>(w);
   w += ((size_t)B * P * 4 + 255) & ~(size_t)255;
   int* n_todo = reinterpret_cast<int*>(w);
+  w += 256;
+  int* first_zero = reinterpret_cast<int*>(w);
   TDSSF_CUDA(cudaMemsetAsync(head, 0xff, (size_t)B * T * 4, s));  // -1: empty bucket
   TDSSF_CUDA(cudaMemsetAsync(n_todo, 0, 4, s));
+  TDSSF_CUDA(cudaMemsetAsync(first_zero, 0x7f, (size_t)B * 4, s));  // 0x7f7f7f7f: no origin row
   const float inv_cell = 1.f / cell;
   const float accept = 0.99f * cell;
   devox_grid_build_kernel<<<dim3((unsigned)ceil_div(V, 256), (unsigned)B), 256, 0, s>>>(vox, vox_stride, V, inv_cell, head,
-                                                                                   T - 1, node);
+                                                                                   T - 1, node, first_zero);
   TDSSF_LAUNCH_CHECK();
   const unsigned qblocks = (unsigned)std::min<int64_t>(ceil_div((int64_t)P * 32, kQueryThreads), (int64_t)num_sms() * 16);
   devox_grid_query_kernel<<<dim3(qblocks, (unsigned)B), kQueryThreads, 0, s>>>(pts, pts_stride, P, V, inv_cell, accept * accept,
-                                                                              head, T - 1, node, idx, todo, n_todo);
+                                                                              head, T - 1, node, first_zero, idx, todo, n_todo);
   TDSSF_LAUNCH_CHECK();
   devox_scan_todo_kernel<<<(unsigned)num_sms() * 8, kScanThreads, 0, s>>>(pts, pts_stride, vox, vox_stride, P, V, todo, n_todo,
                                                                          idx);

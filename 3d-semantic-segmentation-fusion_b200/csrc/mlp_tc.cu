@@ -1094,10 +1094,11 @@ template <typename TokT, bool kGather, bool kSave>
 static int launch_as(const Params& p, cudaStream_t s) {
   auto kern = fused_mlp_kernel<TokT, kGather, kSave>;
   const int smem = kSmemBytes + 1024;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static bool configured[kMaxDevices] = {};  // per instantiation and device (the attribute is per device)
+  const int dev = current_device();
+  if (!configured[dev]) {
     TDSSF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
+    configured[dev] = true;
   }
   const int clusters = std::max(1, std::min(num_sms() / 2, p.n_pairs));
   cudaLaunchConfig_t cfg = {};
@@ -1172,10 +1173,11 @@ static int launch(const Params& p, cudaStream_t s) {
 
 __device__ __align__(16) unsigned char g_zero_rows[4096];  // zero-initialised at module load, never written
 
-static const void* zero_rows() {
-  static void* z = nullptr;
-  if (!z && cudaGetSymbolAddress(&z, g_zero_rows) != cudaSuccess) z = nullptr;
-  return z;
+static const void* zero_rows() {  // a __device__ symbol has one instance per device
+  static void* z[kMaxDevices] = {};
+  const int dev = current_device();
+  if (!z[dev] && cudaGetSymbolAddress(&z[dev], g_zero_rows) != cudaSuccess) z[dev] = nullptr;
+  return z[dev];
 }
 
 // tiles per CTA (upper bound) for N points on this device
@@ -1190,13 +1192,13 @@ static size_t scratch_bytes(int64_t N, int tok_dtype) {
   return table_bytes(N) + (size_t)num_sms() * iters_max_for(N) * kTileM * kCi * (tok_dtype == TDSSF_F32 ? 4 : 2);
 }
 
+__device__ unsigned int g_debug_words[2048];  // [0]: code of a barrier wait that timed out (protocol bug); rest: profile builds
+
 static unsigned int* debug_word() {
-  static unsigned int* d = nullptr;
-  if (!d) {
-    if (cudaMalloc(&d, 8192) != cudaSuccess) return nullptr;
-    cudaMemset(d, 0, 8192);
-  }
-  return d;
+  static void* d[kMaxDevices] = {};
+  const int dev = current_device();
+  if (!d[dev] && cudaGetSymbolAddress(&d[dev], g_debug_words) != cudaSuccess) d[dev] = nullptr;
+  return reinterpret_cast<unsigned int*>(d[dev]);
 }
 
 }  // namespace tc

@@ -7,6 +7,7 @@ CUDA device — there is no CPU or eager fallback.
 from __future__ import annotations
 
 import ctypes as C
+import functools
 from typing import Optional, Sequence
 
 import torch
@@ -33,6 +34,22 @@ def _need_cuda(*tensors):
 
 def _f32c(t: torch.Tensor) -> torch.Tensor:
     return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.to(torch.float32).contiguous()
+
+
+def _on_device(fn):
+    """The library launches on the CURRENT device (and caches per-device state by it), while the stream and the
+    memory belong to the tensors' device: run `fn` with the device of its first CUDA tensor argument current, so a
+    process that drives several GPUs (or a model on cuda:1 without set_device) launches where its data lives."""
+    @functools.wraps(fn)
+    def guarded(*args, **kwargs):
+        for a in args:
+            if torch.is_tensor(a) and a.is_cuda:
+                if a.device.index == torch.cuda.current_device():
+                    break
+                with torch.cuda.device(a.device):
+                    return fn(*args, **kwargs)
+        return fn(*args, **kwargs)
+    return guarded
 
 
 # ------------------------------------------------------------------------------------------------
@@ -81,6 +98,7 @@ def _points_layout(points: torch.Tensor):
 # ------------------------------------------------------------------------------------------------
 # a1-a3
 # ------------------------------------------------------------------------------------------------
+@_on_device
 def project(points, K, Rt, img_hw, encoder=None, *, want_pix=True, want_depth=True, want_valid=True,
             want_flat=False, want_rec=False):
     """points (B,V,>=3) CUDA fp32 (may be a strided view of (B,V,4)); K (B,NC,3,3); Rt (B,NC,4,4);
@@ -108,6 +126,7 @@ def project(points, K, Rt, img_hw, encoder=None, *, want_pix=True, want_depth=Tr
     return out
 
 
+@_on_device
 def scale_pixels(pixel_coords: torch.Tensor, origin_hw: torch.Tensor, new_h: float, new_w: float) -> torch.Tensor:
     """pixel_coords (B,...,2) CUDA fp32; origin_hw (B,2) or (1,2) fp32 on the same device."""
     _need_cuda(pixel_coords, origin_hw)
@@ -124,6 +143,7 @@ def scale_pixels(pixel_coords: torch.Tensor, origin_hw: torch.Tensor, new_h: flo
 # ------------------------------------------------------------------------------------------------
 # a4-a5
 # ------------------------------------------------------------------------------------------------
+@_on_device
 def gather_mean(tokens: torch.Tensor, rec: torch.Tensor) -> torch.Tensor:
     """tokens (B,NC,M,Ci) CUDA fp32/fp16/bf16; rec (B,V,4) int32 records -> (B,V,Ci) fp32."""
     _need_cuda(tokens, rec)
@@ -163,6 +183,7 @@ def _flat_zero_grads(params: Sequence[torch.Tensor]) -> list:
 
 class _MlpF32(torch.autograd.Function):
     @staticmethod
+    @_on_device
     def forward(ctx, x_pt, x_img, W1, b1, W2, b2, W3, b3):
         _need_cuda(x_pt, x_img, W1)
         shape = x_pt.shape[:-1]
@@ -182,6 +203,7 @@ class _MlpF32(torch.autograd.Function):
         return logits.reshape(*shape, 16)
 
     @staticmethod
+    @_on_device
     def backward(ctx, dlogits):
         xp, xi, h1, h2, W1, b1, W2, b2, W3, b3 = ctx.saved_tensors
         N = xp.shape[0]
@@ -203,6 +225,7 @@ def mlp_f32(x_pt, x_img, W1, b1, W2, b2, W3, b3):
     return _MlpF32.apply(x_pt, x_img, W1, b1, W2, b2, W3, b3)
 
 
+@_on_device
 def pack_weights(W1, b1, W2, b2, W3, b3) -> torch.Tensor:
     """bf16 tensor-core operand image of the MLP weights (both CTA ranks + biases)."""
     _need_cuda(W1)
@@ -213,6 +236,7 @@ def pack_weights(W1, b1, W2, b2, W3, b3) -> torch.Tensor:
     return packed
 
 
+@_on_device
 def mlp_tc(x_pt, x_img, packed) -> torch.Tensor:
     """tcgen05 MLP on pre-gathered fp32 features: (N,64),(N,384) -> (N,16)."""
     _need_cuda(x_pt, x_img, packed)
@@ -231,6 +255,7 @@ class _MlpTC(torch.autograd.Function):
     (tdssf_mlp_bwd_tc).  Tolerance 1e-2 (north_star's bf16 bound); `mlp_f32` is the 1e-5 parity mode."""
 
     @staticmethod
+    @_on_device
     def forward(ctx, x_pt, x_img, W1, b1, W2, b2, W3, b3):
         _need_cuda(x_pt, x_img, W1)
         shape = x_pt.shape[:-1]
@@ -251,6 +276,7 @@ class _MlpTC(torch.autograd.Function):
         return logits.reshape(*shape, 16)
 
     @staticmethod
+    @_on_device
     def backward(ctx, dlogits):
         xp, xi, h1, h2, W1, b1, W2, b2, W3, b3 = ctx.saved_tensors
         N = xp.shape[0]
@@ -285,6 +311,7 @@ def _fusion_workspace(device, B, V, tok_code):
     return ws
 
 
+@_on_device
 def fusion_fwd(points, K, Rt, img_hw, encoder, tokens, x_pt, packed, want_rec=False, out=None, preds_out=None,
                save=None):
     """Fully fused inference: points (B,V,>=3), tokens (B,NC,M,384), x_pt (B,V,64) -> logits (B,V,16).
@@ -326,6 +353,7 @@ class _FusedTrain(torch.autograd.Function):
     from the frozen encoder (reference utils/fusion_model.py:68, torch.no_grad) and get no gradient."""
 
     @staticmethod
+    @_on_device
     def forward(ctx, x_pt, W1, b1, W2, b2, W3, b3, points, K, Rt, img_hw, encoder, tokens):
         params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
         _weights_struct(params)  # shape check
@@ -342,6 +370,7 @@ class _FusedTrain(torch.autograd.Function):
         return logits
 
     @staticmethod
+    @_on_device
     def backward(ctx, dlogits):
         xb, h1, h2, W1, b1, W2, b2, W3, b3 = ctx.saved_tensors
         N = xb.shape[0]
@@ -370,6 +399,7 @@ def fusion_train(points, K, Rt, img_hw, encoder, tokens, x_pt, W1, b1, W2, b2, W
 _voxel_ws: dict = {}
 
 
+@_on_device
 def voxelize(points: torch.Tensor, voxel_size: float, knn_cell: Optional[float] = None):
     """points (B,P,3|4) CUDA fp32 -> voxel_raw (B,P,4) fp32 [centroid xyz, 5-NN weighted intensity] with the rows past
     each cloud's voxel count zeroed, voxel_coords (B,P,3) int32, n_voxels (B,) int32 (utils/lidar.py:83-118 for B
@@ -401,6 +431,7 @@ def voxelize(points: torch.Tensor, voxel_size: float, knn_cell: Optional[float] 
 _devox_ws: dict = {}
 
 
+@_on_device
 def devox_nn(pts: torch.Tensor, vox: torch.Tensor, cell: Optional[float] = 0.25) -> torch.Tensor:
     """pts (B,P,>=3), vox (B,V,>=3) CUDA fp32 -> (B,P) int64 nearest-voxel indices (first index on ties).
     `cell`: edge of the search grid's cells in coordinate units (any positive value gives the same indices);
@@ -426,6 +457,7 @@ def devox_nn(pts: torch.Tensor, vox: torch.Tensor, cell: Optional[float] = 0.25)
 
 class _DevoxGather(torch.autograd.Function):
     @staticmethod
+    @_on_device
     def forward(ctx, scores, idx):
         _need_cuda(scores, idx)
         s = _f32c(scores)
@@ -438,6 +470,7 @@ class _DevoxGather(torch.autograd.Function):
         return out
 
     @staticmethod
+    @_on_device
     def backward(ctx, dout):
         (idx,) = ctx.saved_tensors
         B, P, V, Cn = ctx.shape
@@ -457,6 +490,7 @@ def devox_gather(scores: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------
 class _Cels(torch.autograd.Function):
     @staticmethod
+    @_on_device
     def forward(ctx, logits, labels, mask, class_w, lam, ignore_index):
         _need_cuda(logits, labels)
         x = _f32c(logits).reshape(-1, 16)
@@ -478,19 +512,33 @@ class _Cels(torch.autograd.Function):
                                      ws_bytes, _stream(x)), "tdssf_cels_fwd_bwd")
         n = int(n_valid.value)
         ctx.dlog = dlog
+        # kept for a backward through ce / lovasz themselves (tdssf_cels_backward reads the workspace)
+        ctx.terms = (work, w, n_rows, n, float(lam)) if need_grad else None
         ctx.in_shape = tuple(logits.shape)
         ctx.mark_non_differentiable(preds, gt)
+        ctx.set_materialize_grads(False)     # outputs nobody differentiates arrive as None, not as zero tensors
         total, ce, lov, _ = scal.unbind(0)   # `scal` is this call's own buffer: no copies needed
         return total, ce, lov, preds[:n], gt[:n]
 
     @staticmethod
+    @_on_device
     def backward(ctx, g_total, g_ce, g_lov, _gp, _gg):
-        # The kernel produced d total / d logits; ce and lovasz are returned for logging only
-        # (the reference loops call backward on total_loss, utils/train.py:91).
         d = ctx.dlog
-        if d is None:
+        if d is None or (g_total is None and g_ce is None and g_lov is None):
             return None, None, None, None, None, None
-        return (d * g_total).reshape(ctx.in_shape), None, None, None, None, None
+        if g_ce is None and g_lov is None:
+            # the loops call backward on total_loss (utils/train.py:91): the forward call already produced d total
+            return (d * g_total).reshape(ctx.in_shape), None, None, None, None, None
+        # ce_loss / lovasz_loss are differentiable outputs of the reference too (utils/losses.py:60-70):
+        # d = (g_total + g_ce) * d ce + (g_total * lambda + g_lov) * d lovasz, from the kept workspace
+        work, w, n_rows, n, lam = ctx.terms
+        zero = torch.zeros((), dtype=torch.float32, device=d.device)
+        gt_, gc_, gl_ = (zero if g is None else g.to(torch.float32) for g in (g_total, g_ce, g_lov))
+        coef = torch.stack([gt_ + gc_, gt_ * lam + gl_]).contiguous()
+        out = torch.empty_like(d)
+        check(lib.tdssf_cels_backward(_ptr(work), work.numel(), n_rows, n, _ptr(w), _ptr(coef), _ptr(out), _stream(out)),
+              "tdssf_cels_backward")
+        return out.reshape(ctx.in_shape), None, None, None, None, None
 
 
 def cels(logits, labels, mask, class_w, lam=1.0, ignore_index=0):
@@ -501,6 +549,7 @@ def cels(logits, labels, mask, class_w, lam=1.0, ignore_index=0):
 # ------------------------------------------------------------------------------------------------
 # a11
 # ------------------------------------------------------------------------------------------------
+@_on_device
 def confusion(preds: torch.Tensor, labels: torch.Tensor, num_classes: int, out: Optional[torch.Tensor] = None):
     """int64 (C,C) confusion matrix, rows = truth; accumulates into `out` when given."""
     _need_cuda(preds, labels)
@@ -537,11 +586,13 @@ def compose_lidar2cam(lidar_sensor, cam_sensor, lidar_ego=None, cam_ego=None, de
     B, NC = cs.shape[0], cs.shape[1]
     out32 = torch.empty((B, NC, 4, 4), dtype=torch.float32, device=ls.device)
     out64 = torch.empty((B, NC, 4, 4), dtype=torch.float64, device=ls.device) if want_f64 else None
-    check(lib.tdssf_compose_lidar2cam(_ptr(ls), _ptr(cs), _ptr(le), _ptr(ce), B, NC, _ptr(out32), _ptr(out64), _stream(ls)),
-          "tdssf_compose_lidar2cam")
+    with torch.cuda.device(ls.device):
+        check(lib.tdssf_compose_lidar2cam(_ptr(ls), _ptr(cs), _ptr(le), _ptr(ce), B, NC, _ptr(out32), _ptr(out64),
+                                          _stream(ls)), "tdssf_compose_lidar2cam")
     return (out32, out64) if want_f64 else out32
 
 
+@_on_device
 def accumulate_sweeps(points, counts, sweep_sensor, sweep_ego, ref_sensor, ref_ego):
     """points (S,P,4) fp32 CUDA (padded sweeps), counts (S,) valid rows; poses as in compose_lidar2cam ->
     (cloud (S*P,4) fp32 with the first `total` rows filled in sweep order, total (1,) int32 on the device,

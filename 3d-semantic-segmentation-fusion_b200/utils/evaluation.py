@@ -17,23 +17,36 @@ def _marginals(cm: torch.Tensor):
 def compute_confusion_matrix(preds, labels, num_classes, out=None):
     """preds, labels in 1..C on any device (host tensors are uploaded once — the reference's loops hand
     CPU tensors here, utils/test.py:82-87).  Returns the int64 (C,C) matrix, rows = truth, on the inputs'
-    device.  `out` (CUDA int64 (C,C)) accumulates across calls without leaving the device."""
+    device.  `out` (CUDA int64 (C,C)) accumulates across calls without leaving the device.
+
+    Values outside 1..C (torch.bincount would raise on a negative index and grow the matrix on a large one,
+    utils/evaluation.py:38-40) raise RuntimeError.  The check never adds a device synchronisation to a loop:
+    host inputs are checked on the host before the upload; device inputs without `out` are checked through the one
+    scalar the caller is about to read anyway (the matrix total); with `out` the kernel drops such pairs and the
+    caller can compare `out.sum()` with its own point count after the last batch."""
     if not torch.cuda.is_available():
         raise RuntimeError("tdssf confusion matrix runs on a CUDA device only (no CPU fallback)")
     home = preds.device
     dev = out.device if out is not None else (home if preds.is_cuda else torch.device("cuda"))
-    if preds.numel():
+    n = preds.numel()
+    if n and not preds.is_cuda and not labels.is_cuda:
         lo = min(int(preds.min()), int(labels.min()))
         hi = max(int(preds.max()), int(labels.max()))
-        if lo < 1 or hi > num_classes:  # torch.bincount would raise / grow on these
+        if lo < 1 or hi > num_classes:
             raise RuntimeError(f"confusion matrix: values must lie in 1..{num_classes} (got {lo}..{hi})")
     cm = ops.confusion(preds.to(dev), labels.to(dev), num_classes, out=out)
-    return cm if out is not None else cm.to(home)
+    if out is not None:
+        return cm
+    if n and (preds.is_cuda or labels.is_cuda) and int(cm.sum()) != n:
+        raise RuntimeError(f"confusion matrix: {n - int(cm.sum())} of {n} pairs lie outside 1..{num_classes}")
+    return cm.to(home)
 
 
 def compute_iou(conf_matrix):
-    hit, truth, predicted = _marginals(conf_matrix)
-    iou = hit / (truth + predicted - hit).clamp(min=1)
+    # the union is formed in int64 like the reference (utils/evaluation.py:46-49): exact beyond 2^24 points
+    hit = torch.diag(conf_matrix)
+    union = conf_matrix.sum(dim=1) + conf_matrix.sum(dim=0) - hit
+    iou = hit.float() / union.float().clamp(min=1)
     return iou, iou.mean()
 
 
@@ -44,15 +57,16 @@ def per_class_accuracy(conf_matrix):
 
 
 def overall_accuracy(conf_matrix):
-    hit, truth, _ = _marginals(conf_matrix)
-    return hit.sum() / truth.sum().clamp(min=1)
+    # integer sums first, one conversion each (utils/evaluation.py:59-62)
+    return torch.diag(conf_matrix).sum().float() / conf_matrix.sum().float().clamp(min=1)
 
 
 def precision_recall_f1(conf_matrix):
     hit, truth, predicted = _marginals(conf_matrix)
-    # tp + fp = column sum, tp + fn = row sum
-    precision = (hit / predicted.clamp(min=1)).mean()
-    recall = (hit / truth.clamp(min=1)).mean()
+    # the reference forms fp = column sum - tp and fn = row sum - tp in fp32 and adds tp back (utils/evaluation.py:66-71);
+    # the same two roundings are kept so that the macro averages agree bit for bit
+    precision = (hit / (hit + (predicted - hit)).clamp(min=1)).mean()
+    recall = (hit / (hit + (truth - hit)).clamp(min=1)).mean()
     f1 = 2 * precision * recall / (precision + recall).clamp(min=1e-6)
     return precision, recall, f1
 

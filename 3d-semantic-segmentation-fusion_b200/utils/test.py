@@ -1,4 +1,6 @@
-"""Drop-in for the evaluation loop of the reference's utils/test.py (`test_model`, utils/test.py:12-91), SURVEY f3.
+"""Drop-in for the evaluation loops of the reference's utils/test.py (`test_model`, utils/test.py:12-91, and
+`test_sample`, utils/test.py:93-173), SURVEY f3.  The reference's own utils/test.py also runs unchanged over the other
+drop-in modules (tests/test_reference_loops.py); this module is the variant that keeps the statistics on the device.
 
 Same signature, same printed report and returned dict (through utils.evaluation).  What changes is where the
 statistics live: the reference appends every batch's predictions and labels to host lists (a D2H copy + sync per
@@ -86,3 +88,50 @@ def test_model(dataloaders, image_encoder, pcd_encoder, model, criterion, device
         iterations = int(parallel.sum_over_ranks(iterations, device))
     total_loss, total_correct, total_points = stats.tolist()                       # the one host read
     return _report(cm, total_loss, total_correct, total_points, iterations)
+
+
+@torch.no_grad()
+def test_sample(config, dataloaders, image_encoder, pcd_encoder, model, criterion, device):
+    """One batch of dataloaders['test'] through the model, metrics + the scene arrays (utils/test.py:93-173).
+    The projection plot is drawn by the reference's utils.plot when that module (matplotlib / plotly / cv2) is
+    importable; the returned dict is the same either way."""
+    model.eval()
+    device = torch.device(device)
+    batch = next(iter(dataloaders["test"]))
+    images, image_sizes, lidar_points, labels, mask, cam_intrinsics, lidar2cam_extrinsics = batch
+    images = images.to(device)
+    image_sizes = image_sizes.to(device)
+    lidar_points = lidar_points.to(device)
+    labels = labels.to(device)
+    mask = mask.to(device)
+    cam_intrinsics = [c.to(device) for c in cam_intrinsics]
+    lidar2cam_extrinsics = [c.to(device) for c in lidar2cam_extrinsics]
+
+    views = [image_encoder(images[:, v])["patch_features"] for v in range(images.shape[1])]
+    patch_tokens = torch.stack(views, dim=1)
+    voxel_features, voxel_raw, voxel_coords, voxel_mask = pcd_encoder(lidar_points)
+    outputs = model(patch_tokens, voxel_features, voxel_raw, voxel_coords, image_sizes, cam_intrinsics,
+                    lidar2cam_extrinsics)
+    combined_loss, ce_loss, lovasz_loss, predictions, gt_labels_valid = criterion(outputs, labels, mask=mask)
+
+    num_classes = outputs.shape[-1]
+    cm = torch.zeros((num_classes, num_classes), dtype=torch.int64, device=device)
+    if predictions.numel():
+        ops.confusion(predictions, gt_labels_valid, num_classes, out=cm)
+    total_correct = (predictions == gt_labels_valid).sum().double()
+    total_points = gt_labels_valid.size(0)
+    metrics = _report(cm, combined_loss, total_correct, total_points, 1)
+
+    valid_pts = lidar_points[0][mask.bool()[0]]            # (N_valid, 4), first sample like the reference
+    all_preds, all_labels = predictions.cpu(), gt_labels_valid.cpu()
+    results = {**metrics, "points": valid_pts.cpu().numpy(), "predictions": all_preds, "labels": all_labels}
+    try:
+        from utils.plot import plot_images_with_point_cloud
+    except ImportError:
+        plot_images_with_point_cloud = None
+    if plot_images_with_point_cloud is not None:
+        plot_images_with_point_cloud(config=config, images=images, points=valid_pts, pred_labels=all_preds,
+                                     gt_labels=all_labels, cam_intrinsics=cam_intrinsics,
+                                     lidar2cam_extrinsics=lidar2cam_extrinsics,
+                                     save_dir=config['test_params']['checkpoint_path'])
+    return results

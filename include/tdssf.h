@@ -255,6 +255,13 @@ TDSSF_API int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, con
                        float* out_scalars, int64_t* n_valid_host, int64_t* preds, int64_t* gt,
                        float* dlogits, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Backward through the individual terms (the reference's three loss outputs are all differentiable, utils/losses.py:60-70):
+ * dlogits = coef[0] * d ce / d logits + coef[1] * d lovasz / d logits, from the workspace a tdssf_cels_fwd_bwd call on the
+ * same n_rows left behind (probabilities, Jaccard gradients, per-class counts; the caller keeps it alive and unmodified).
+ * coef: device float[2].  n_valid: the value that call returned in n_valid_host.  dlogits [n_rows,16] is overwritten. */
+TDSSF_API int tdssf_cels_backward(const void* workspace, size_t workspace_bytes, int64_t n_rows, int64_t n_valid,
+                                  const float* class_w, const float* coef, float* dlogits, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * a11  confusion matrix
  * replaces  compute_confusion_matrix   utils/evaluation.py:35-42

@@ -2,9 +2,12 @@
 
     python tests/golden/make_golden.py            # needs /root/reference (build container only)
 
-The reference (CharlesChang012/3D-Semantic-Segmentation-Fusion @ e5103fd) is imported unmodified
-from /root/reference: utils.fusion_model (multi_camera_projector, scale_pixel_coords,
-FeatureFusionModel), utils.losses.CELSLoss, LovaszSoftmax.pytorch.lovasz_losses, utils.evaluation.
+The reference (CharlesChang012/3D-Semantic-Segmentation-Fusion @ e5103fd) is loaded unmodified, BY FILE PATH,
+from /root/reference through oracle/ref_loader.py: utils/fusion_model.py (multi_camera_projector,
+scale_pixel_coords, FeatureFusionModel), utils/losses.py (CELSLoss), LovaszSoftmax/pytorch/lovasz_losses.py,
+utils/evaluation.py.  (A plain `import utils.fusion_model` would resolve to this repository's drop-in package of
+the same name; the loader asserts every module's __file__ lies under the reference root.)
+tests/test_golden_regen.py re-runs this script into a temporary directory and requires bit-identical files.
 utils/lidar.py cannot be imported (open3d / spconv absent), so the devoxelize golden re-executes its
 torch statements (utils/lidar.py:147-155) verbatim on CPU.
 
@@ -25,10 +28,12 @@ import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
-sys.path.insert(0, os.path.join(ROOT, "3d-semantic-segmentation-fusion_b200"))
-from tdssf import synth  # noqa: E402
+sys.path[:0] = [ROOT, os.path.join(ROOT, "3d-semantic-segmentation-fusion_b200")]
+from tdssf import synth  # noqa: E402  (seeded input generators only: no kernel is involved)
+from oracle import ref_loader  # noqa: E402
 
-REF = os.environ.get("TDSSF_REFERENCE", "/root/reference")
+OUT = HERE   # --out redirects (tests/test_golden_regen.py)
+REFM = None  # the reference's modules, set by main()
 
 
 def checksum(*arrays):
@@ -52,7 +57,8 @@ class StubPcd(torch.nn.Module):
 
 
 def run_fusion_case(name, B, V, encoder, seed, tok_dtype=torch.float32, stride=16):
-    from utils.fusion_model import FeatureFusionModel, multi_camera_projector, scale_pixel_coords
+    FeatureFusionModel, multi_camera_projector, scale_pixel_coords = (
+        REFM.fusion_model.FeatureFusionModel, REFM.fusion_model.multi_camera_projector, REFM.fusion_model.scale_pixel_coords)
     sw = synth.make_sweeps(B, V, encoder, seed=seed, tok_dtype=tok_dtype)
     enc = sw.encoder
     w = synth.make_mlp_weights(seed)
@@ -77,7 +83,7 @@ def run_fusion_case(name, B, V, encoder, seed, tok_dtype=torch.float32, stride=1
     fused_in = captured["x"]
     img_feat = fused_in[..., 64:]
     np.savez_compressed(
-        os.path.join(HERE, name + ".npz"),
+        os.path.join(OUT, name + ".npz"),
         B=B, V=V, seed=seed, encoder=encoder, tok_dtype=str(tok_dtype).replace("torch.", ""),
         input_checksum=sweeps_checksum(sw), stride=stride,
         pixel_coords=pix.numpy(), depth=depth.numpy(), valid=valid.numpy(),
@@ -94,7 +100,7 @@ def run_fusion_case(name, B, V, encoder, seed, tok_dtype=torch.float32, stride=1
 
 def run_kat_projection():
     """Hand-checkable projection cases: identity extrinsic, pinhole K, points on the image borders."""
-    from utils.fusion_model import multi_camera_projector
+    multi_camera_projector = REFM.fusion_model.multi_camera_projector
     f, cx, cy, H, W = 1000.0, 800.0, 450.0, 900, 1600
     K = torch.tensor([[f, 0, cx], [0, f, cy], [0, 0, 1.0]]).repeat(2, 1, 1)
     Rt = torch.eye(4).repeat(2, 1, 1)
@@ -109,14 +115,14 @@ def run_kat_projection():
     pts = torch.tensor(pts, dtype=torch.float32)[None]
     with torch.no_grad():
         pix, depth, valid = multi_camera_projector(pts, [K], [Rt], torch.tensor([[H, W]]))
-    np.savez_compressed(os.path.join(HERE, "kat_projection.npz"), points=pts.numpy(), K=K.numpy()[None],
+    np.savez_compressed(os.path.join(OUT, "kat_projection.npz"), points=pts.numpy(), K=K.numpy()[None],
                         Rt=Rt.numpy()[None], image_sizes=np.array([[H, W]]), pixel_coords=pix.numpy(),
                         depth=depth.numpy(), valid=valid.numpy())
     print("kat_projection: valid =", valid[0].int().tolist())
 
 
 def run_mlp_backward(seed=5, B=2, V=192):
-    from utils.fusion_model import FeatureFusionModel
+    FeatureFusionModel = REFM.fusion_model.FeatureFusionModel
     gen = torch.Generator().manual_seed(seed)
     x_pt = torch.randn(B, V, 64, generator=gen, requires_grad=True)
     x_img = torch.randn(B, V, 384, generator=gen)
@@ -127,14 +133,14 @@ def run_mlp_backward(seed=5, B=2, V=192):
     out = model.mlp(torch.cat([x_pt, x_img], dim=-1))
     (out * G).sum().backward()
     np.savez_compressed(
-        os.path.join(HERE, "mlp_backward.npz"), seed=seed, x_pt=x_pt.detach().numpy(), x_img=x_img.numpy(),
+        os.path.join(OUT, "mlp_backward.npz"), seed=seed, x_pt=x_pt.detach().numpy(), x_img=x_img.numpy(),
         G=G.numpy(), logits=out.detach().numpy(), dx_pt=x_pt.grad.numpy(),
         **{"grad_" + k: p.grad.numpy() for k, p in model.mlp.named_parameters()})
     print("mlp_backward: |dW1| =", float(model.mlp[0].weight.grad.norm()))
 
 
 def run_cels(name, B, P, seed, mask_mode="equal", lam=1.0, scale=2.0):
-    from utils.losses import CELSLoss
+    CELSLoss = REFM.losses.CELSLoss
     gen = torch.Generator().manual_seed(seed)
     logits = (torch.randn(B, P, 16, generator=gen) * scale).requires_grad_(True)
     labels = synth.make_labels(B, P, gen)
@@ -148,7 +154,7 @@ def run_cels(name, B, P, seed, mask_mode="equal", lam=1.0, scale=2.0):
         total, ce, lov, preds, gt = crit(logits, labels, mask)
     total.backward()
     np.savez_compressed(
-        os.path.join(HERE, name + ".npz"), logits=logits.detach().numpy(), labels=labels.numpy(),
+        os.path.join(OUT, name + ".npz"), logits=logits.detach().numpy(), labels=labels.numpy(),
         mask=(mask.numpy() if mask is not None else np.zeros(0, dtype=bool)), has_mask=mask is not None,
         lam=lam, total=total.item(), ce=ce.item(), lovasz=lov.item(), preds=preds.numpy(), gt=gt.numpy(),
         dlogits=logits.grad.numpy(), class_weights=np.array(synth.CLASS_WEIGHTS, dtype=np.float32))
@@ -156,7 +162,7 @@ def run_cels(name, B, P, seed, mask_mode="equal", lam=1.0, scale=2.0):
 
 
 def run_lovasz_small():
-    from LovaszSoftmax.pytorch.lovasz_losses import lovasz_grad, lovasz_softmax_flat
+    lovasz_grad, lovasz_softmax_flat = REFM.lovasz_losses.lovasz_grad, REFM.lovasz_losses.lovasz_softmax_flat
     cases = {}
     gt_sorted = torch.tensor([1.0, 0.0, 1.0, 0.0])
     cases["grad_1010"] = lovasz_grad(gt_sorted).numpy()
@@ -168,13 +174,14 @@ def run_lovasz_small():
     cases["loss"] = np.float32(lovasz_softmax_flat(probas, labels).item())
     empty = lovasz_softmax_flat(torch.zeros(0, 3), torch.zeros(0, dtype=torch.long))
     cases["empty_shape"] = np.array(empty.shape)
-    np.savez_compressed(os.path.join(HERE, "lovasz_small.npz"), **cases)
+    np.savez_compressed(os.path.join(OUT, "lovasz_small.npz"), **cases)
     print("lovasz_small: loss", cases["loss"], "grad", cases["grad_1010"])
 
 
 def run_confusion(seed=11, n=50_000):
-    from utils.evaluation import (compute_confusion_matrix, compute_iou, per_class_accuracy, overall_accuracy,
-                                  precision_recall_f1)
+    E = REFM.evaluation
+    compute_confusion_matrix, compute_iou, per_class_accuracy, overall_accuracy, precision_recall_f1 = (
+        E.compute_confusion_matrix, E.compute_iou, E.per_class_accuracy, E.overall_accuracy, E.precision_recall_f1)
     gen = torch.Generator().manual_seed(seed)
     labels = synth.make_labels(1, n, gen).view(-1)
     labels = labels[labels != 0]
@@ -184,7 +191,7 @@ def run_confusion(seed=11, n=50_000):
     iou, miou = compute_iou(cm)
     acc, macc = per_class_accuracy(cm)
     pr, rc, f1 = precision_recall_f1(cm)
-    np.savez_compressed(os.path.join(HERE, "confusion.npz"), preds=preds.numpy(), labels=labels.numpy(),
+    np.savez_compressed(os.path.join(OUT, "confusion.npz"), preds=preds.numpy(), labels=labels.numpy(),
                         cm=cm.numpy(), iou=iou.numpy(), miou=miou.item(), acc=acc.numpy(), macc=macc.item(),
                         oa=overall_accuracy(cm).item(), precision=pr.item(), recall=rc.item(), f1=f1.item())
     print("confusion: mIoU", miou.item())
@@ -206,15 +213,21 @@ def run_devox(seed=13, B=2, P=3000, V=2200, pad=100):
         d = torch.cdist(pts[b][:, :3], vox[b][:, :3])
         idx[b] = torch.argmin(d, dim=1)
         out[b] = scores[b, :V][idx[b]]
-    np.savez_compressed(os.path.join(HERE, "devox.npz"), pts=pts.numpy(), vox=vox.numpy(), scores=scores.numpy(),
+    np.savez_compressed(os.path.join(OUT, "devox.npz"), pts=pts.numpy(), vox=vox.numpy(), scores=scores.numpy(),
                         idx=idx.numpy(), out=out.numpy())
     print("devox: points mapped to a padded (zero) voxel:", int((idx >= V - pad).sum()))
 
 
-def main():
-    if not os.path.isdir(REF):
-        raise SystemExit(f"{REF} not found: goldens can only be regenerated where the reference is mounted")
-    sys.path.insert(0, REF)
+def main(out=None):
+    global OUT, REFM
+    root = ref_loader.ref_root(allow_copy=False)  # the mounted tree only: goldens are never made from a copy
+    if root is None:
+        raise SystemExit("reference tree not found: goldens can only be regenerated where the reference is mounted")
+    REFM = ref_loader.load_hot_path(root)
+    for mod in (REFM.fusion_model, REFM.losses, REFM.evaluation, REFM.lovasz_losses):
+        assert os.path.abspath(mod.__file__).startswith(os.path.abspath(root) + os.sep), mod.__file__
+    OUT = out or HERE
+    os.makedirs(OUT, exist_ok=True)
     warnings.filterwarnings("ignore", category=SyntaxWarning)
     torch.manual_seed(0)
     run_kat_projection()
@@ -233,4 +246,7 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=None, help="write the .npz files here instead of tests/golden/")
+    main(ap.parse_args().out)

@@ -6,12 +6,15 @@ Tolerances (north_star): bit-exact for pixel coordinates, masks, patch indices, 
 matrices and sort-dependent integer results; 1e-5 relative for fp32 features / logits / loss."""
 import hashlib
 import os
+import sys
 
 import numpy as np
 import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 from oracle import np_oracle as O  # noqa: E402
 from tdssf import synth  # noqa: E402
@@ -444,39 +447,13 @@ def test_evaluation_loop_dropin(ops, capsys):
     from utils.evaluation import evaluate
     from utils.fusion_model import FeatureFusionModel
     from utils.losses import CELSLoss
+    import harness
     n_batches, B, V = 3, 2, 3000
-    sweeps = [synth.make_sweeps(B, V, "dinov2", seed=50 + i) for i in range(n_batches)]
-
-    class ImageEncoder:   # stands in for DINO: the "image" carries the index of its pre-computed token map
-        patch_size, resize_height, resize_width = sweeps[0].encoder.patch_size, sweeps[0].encoder.resize_height, sweeps[0].encoder.resize_width
-
-        def __call__(self, images):
-            out = []
-            for img in images:
-                i, b, v = (int(x) for x in img.flatten()[:3])
-                out.append(sweeps[i].tokens[b, v].cuda())
-            return {"patch_features": torch.stack(out), "global_features": None}
-
-    class Pcd(torch.nn.Module):
-        def forward(self, pts):
-            self.feat = torch.cat([pts, pts.flip(-1)] * 8, -1)[..., :64].contiguous()
-            return self.feat, pts, None, None
-
-        def devoxelize(self, s):
-            return s, None
-
-    def batch(i):
-        sw = sweeps[i]
-        images = torch.zeros(B, 6, 3, 1, 1)
-        for b in range(B):
-            for v in range(6):
-                images[b, v, :, 0, 0] = torch.tensor([i, b, v], dtype=torch.float32)
-        return images, sw.image_sizes, sw.points, sw.labels, sw.mask, sw.K, sw.Rt
-
-    loaders = {"test": [batch(i) for i in range(n_batches)]}
-    enc, pcd = ImageEncoder(), Pcd()
+    sweeps, batches = harness.make_batches(n_batches, B, V, seed=50)
+    loaders = {"test": batches}
+    enc, pcd = harness.TokenLookupEncoder(sweeps, device="cuda"), harness.IdentityVoxels().cuda()
     model = FeatureFusionModel(enc, pcd, device="cuda").cuda()
-    model.load_state_dict(synth.make_mlp_weights(50), strict=True)
+    model.load_state_dict({**synth.make_mlp_weights(50), "pcd_encoder.scale": torch.ones(64)}, strict=True)
     crit = CELSLoss(weight=torch.tensor(synth.CLASS_WEIGHTS).cuda())
     got = eval_loop.test_model(loaders, enc, pcd, model, crit, "cuda")
     assert "EVALUATION METRICS" in capsys.readouterr().out
