@@ -1,100 +1,61 @@
-// a6 backward in bf16 (training with the tensor-core forward): the gradients of the 448->256->64->16 MLP from the bf16
-// activations tdssf_mlp_fwd_tc saved.  Replaces the autograd of FeatureFusionModel.mlp (utils/fusion_model.py:144-150,
-// 203-204; utils/train.py:91 calls backward on the total loss).
+// a6 backward on the 5th-generation tensor cores (tcgen05, bf16 operands, fp32 accumulate in TMEM): the gradients of
+// the 448->256->64->16 MLP from the bf16 rows / activations the tcgen05 forward saved.  Replaces the autograd of
+// FeatureFusionModel.mlp (utils/fusion_model.py:144-150,203-204; utils/train.py:91 calls backward on the total loss).
+// Every product is a kernel of this file; no vendor GEMM library is involved.
 //
-// The six matrix products are plain GEMMs (no fusion with a gather, no special layout), so they go to cuBLAS
-// (cublasGemmEx, bf16 operands, fp32 accumulate, fp32 outputs accumulated in place); hand-written here are the
-// element-wise kernels around them: fp32 -> bf16 conversion with the [x_pt | x_img] concatenation, the ReLU masks with
-// the bias-gradient column sums, and the orchestration.  cuBLAS is loaded at first use (dlopen), so libtdssf.so itself
-// has no link-time dependency on it.
+//   dl   = dlogits                               db3 += sum_rows dl          dW3 += dl^T  @ h2
+//   dh2  = (dl  @ W3) * (h2 > 0)     [N,64]      db2 += sum_rows dh2         dW2 += dh2^T @ h1
+//   dh1  = (dh2 @ W2) * (h1 > 0)     [N,256]     db1 += sum_rows dh1         dW1 += dh1^T @ [x_pt | x_img]
+//   dx_pt = dh1 @ W1[:, :64]         [N,64]
 //
-//   dl   = bf16(dlogits)                         db3 += sum_rows dlogits
-//   G2   = dl  @ W3            [N,64]            dh2 = G2 * (h2 > 0)     db2 += sum_rows dh2
-//   G1   = dh2 @ W2            [N,256]           dh1 = G1 * (h1 > 0)     db1 += sum_rows dh1
-//   dx_pt = dh1 @ W1[:, :64]   [N,64]
-//   dW3 += dl^T @ h2     dW2 += dh2^T @ h1     dW1 += dh1^T @ [x_pt | x_img]
-#include <cublas_v2.h>
+// Three launches after the operand packing:
+//   dgrad_chain_kernel   the data-gradient chain per 128-point tile: dl @ W3 on the CUDA cores (K = 16), dh2 @ W2 and
+//                        dh1 @ W1[:, :64] as tcgen05.mma with the weights resident in shared memory, the ReLU masks in
+//                        the TMEM epilogues (the h1 tile arrives by TMA and is overwritten in place by dh1, which is the
+//                        A operand of the next product), bias sums and the bf16 copies of dh2 / dh1 for the weight
+//                        gradients written from shared memory by two helper warps.  Bound: HBM (about 223 MB per 4 sweeps).
+//   dw3_db3_kernel       dW3 (16 x 64, 0.3 GFLOP) and db3 on the CUDA cores.
+//   wgrad_kernel         dW1 and dW2 with the points as the K dimension: both operands are the row-major [points, features]
+//                        matrices as they lie in HBM, i.e. MN-major UMMA operands, delivered by TMA into 128B-swizzled
+//                        slabs; every CTA accumulates its share of the points into TMEM (512 columns, all used) and writes
+//                        one fp32 partial; wgrad_reduce_kernel adds the partials into the caller's buffers in a fixed
+//                        order (deterministic).  Two CTA flavours split the 448 input columns so that each accumulator
+//                        set fits TMEM:  A: dW1[:, 0:256]   B: dW1[:, 256:448] and dW2^T.
+#include <cuda.h>
 #include <cuda_bf16.h>
-#include <dlfcn.h>
 
-#include <mutex>
+#include <algorithm>
 
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace tdssf {
 namespace bwd {
 
 constexpr int kCp = 64, kCi = 384, kK1 = 448, kN1 = 256, kN2 = 64, kC = 16;
 
-// ---- cuBLAS, resolved at first use ----------------------------------------------------------------------------
-struct Cublas {
-  void* lib = nullptr;
-  cublasStatus_t (*create)(cublasHandle_t*) = nullptr;
-  cublasStatus_t (*set_stream)(cublasHandle_t, cudaStream_t) = nullptr;
-  cublasStatus_t (*gemm_ex)(cublasHandle_t, cublasOperation_t, cublasOperation_t, int, int, int, const void*, const void*,
-                            cudaDataType, int, const void*, cudaDataType, int, const void*, void*, cudaDataType, int,
-                            cublasComputeType_t, cublasGemmAlgo_t) = nullptr;
-  cublasHandle_t handle[64] = {};
-  bool ok = false;
-};
-
-static Cublas& cublas() {
-  static Cublas c;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    for (const char* name : {"libcublas.so.12", "libcublas.so", "/usr/local/cuda/lib64/libcublas.so.12"}) {
-      c.lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
-      if (c.lib) break;
-    }
-    if (!c.lib) return;
-    c.create = reinterpret_cast<decltype(c.create)>(dlsym(c.lib, "cublasCreate_v2"));
-    c.set_stream = reinterpret_cast<decltype(c.set_stream)>(dlsym(c.lib, "cublasSetStream_v2"));
-    c.gemm_ex = reinterpret_cast<decltype(c.gemm_ex)>(dlsym(c.lib, "cublasGemmEx"));
-    c.ok = c.create && c.set_stream && c.gemm_ex;
-  });
-  return c;
-}
-
-static cublasHandle_t handle_for_current_device() {
-  static std::mutex mu;
-  Cublas& c = cublas();
-  if (!c.ok) return nullptr;
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::lock_guard<std::mutex> lock(mu);
-  if (!c.handle[dev] && c.create(&c.handle[dev]) != CUBLAS_STATUS_SUCCESS) c.handle[dev] = nullptr;
-  return c.handle[dev];
-}
-
-// row-major C[m,n] (ldc) = alpha * op(A) op(B) + beta * C, A and B bf16 row-major, C fp32 (or bf16: c_bf16), fp32 accumulate
-static cublasStatus_t gemm_rm(cublasHandle_t h, bool ta, bool tb, int m, int n, int k, float alpha, const void* A, int lda,
-                              const void* B, int ldb, float beta, void* C, int ldc, bool c_bf16 = false) {
-  // row-major X is column-major X^T: C^T = op(B)^T op(A)^T
-  return cublas().gemm_ex(h, tb ? CUBLAS_OP_T : CUBLAS_OP_N, ta ? CUBLAS_OP_T : CUBLAS_OP_N, n, m, k, &alpha, B, CUDA_R_16BF,
-                          ldb, A, CUDA_R_16BF, lda, &beta, C, c_bf16 ? CUDA_R_16BF : CUDA_R_32F, ldc, CUBLAS_COMPUTE_32F,
-                          CUBLAS_GEMM_DEFAULT);
-}
-
-// ---- element-wise kernels -----------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+// bf16 > 0  <=>  sign clear and not zero, for the two halves of a packed word: 0xffff / 0 per half
+__device__ __forceinline__ uint32_t relu_mask2(uint32_t h) {
+  const uint32_t lo = h & 0xffffu, hi = h >> 16;
+  return ((lo != 0u && !(lo & 0x8000u)) ? 0x0000ffffu : 0u) | ((hi != 0u && !(hi & 0x8000u)) ? 0xffff0000u : 0u);
+}
 
-// dst[i] = bf16(src[i]), 8 elements per thread (every count is a multiple of 8);
-// the three weight matrices in one launch (the training step is bound by the host's launches, not by this kernel)
-__global__ void cvt3_bf16_kernel(const float* __restrict__ s0, uint4* __restrict__ d0, int64_t n0, const float* __restrict__ s1,
-                                 uint4* __restrict__ d1, int64_t n1, const float* __restrict__ s2, uint4* __restrict__ d2, int64_t n2) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1 + n2; i += (int64_t)gridDim.x * blockDim.x) {
-    const float* src = i < n0 ? s0 : i < n0 + n1 ? s1 : s2;
-    uint4* dst = i < n0 ? d0 : i < n0 + n1 ? d1 : d2;
-    const int64_t k = i < n0 ? i : i < n0 + n1 ? i - n0 : i - n0 - n1;
-    const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * k), b = __ldg(reinterpret_cast<const float4*>(src) + 2 * k + 1);
-    dst[k] = make_uint4(pack2(a.x, a.y), pack2(a.z, a.w), pack2(b.x, b.y), pack2(b.z, b.w));
+__device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity) {
+  if (ptx::mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!ptx::mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) __trap();  // ~2 s: a protocol bug, never a legitimate wait
   }
 }
 
-// X[r, 0:64] = bf16(x_pt[r]), X[r, 64:448] = bf16(x_img[r]); one thread per 8 columns
+// X[r, 0:64] = bf16(x_pt[r]), X[r, 64:448] = bf16(x_img[r]); one thread per 8 columns (only for the unfused forward,
+// which saves no bf16 input rows)
 __global__ void concat_bf16_kernel(const float* __restrict__ x_pt, const float* __restrict__ x_img, uint4* __restrict__ X, int64_t N) {
   const int64_t total = N * (kK1 / 8);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -106,94 +67,595 @@ __global__ void concat_bf16_kernel(const float* __restrict__ x_pt, const float* 
   }
 }
 
-// out = bf16(G * (h > 0)) (h == nullptr: no mask), db[c] += column sums of the masked values.  G is fp32 (the loss
-// gradient) or bf16 (a data-gradient GEMM that wrote bf16 straight into `out`: in place, half the traffic of an fp32
-// round trip, and the same bits - the mask is 0/1, so rounding before or after it is the same rounding).
-// Block = 256 threads = 32 rows x 8 column groups per pass over a [N, C] matrix, C in {16, 64, 256}: thread (ty, tx)
-// walks rows ty, ty+32, ... of its grid-stride slice and columns 8*tx + 64*j.
-template <int C, typename GT>
-__global__ void __launch_bounds__(256)
-mask_cvt_colsum_kernel(const GT* G, const uint16_t* __restrict__ h, uint16_t* out, float* __restrict__ db, int64_t N) {
-  constexpr int kGroups = C / 8;                      // 8-column groups per row
-  constexpr int kTx = kGroups < 8 ? kGroups : 8;      // column groups handled side by side
-  constexpr int kTy = 256 / kTx;
-  constexpr int kJ = kGroups / kTx;
-  const int tx = threadIdx.x % kTx, ty = threadIdx.x / kTx;
-  float acc[kJ][8];
-#pragma unroll
-  for (int j = 0; j < kJ; ++j)
-#pragma unroll
-    for (int e = 0; e < 8; ++e) acc[j][e] = 0.f;
-  for (int64_t r = (int64_t)blockIdx.x * kTy + ty; r < N; r += (int64_t)gridDim.x * kTy) {
-#pragma unroll
-    for (int j = 0; j < kJ; ++j) {
-      const int c = (tx + j * kTx) * 8;
-      float v[8];
-      if (sizeof(GT) == 4) {
-        const float4* g4 = reinterpret_cast<const float4*>(G + r * C + c);
-        const float4 a = g4[0], b = g4[1];
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-      } else {
-        const uint4 q = *reinterpret_cast<const uint4*>(G + r * C + c);
-        const uint32_t g[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float((e & 1) ? (g[e >> 1] & 0xffff0000u) : (g[e >> 1] << 16));
-      }
-      if (h) {
-        const uint4 m = __ldg(reinterpret_cast<const uint4*>(h + r * C + c));
-        const uint32_t w[4] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const uint32_t bits = (w[e >> 1] >> ((e & 1) * 16)) & 0xffffu;   // bf16 > 0  <=>  sign clear and not zero
-          if (bits == 0u || (bits & 0x8000u)) v[e] = 0.f;
-        }
-      }
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[j][e] += v[e];
-      *reinterpret_cast<uint4*>(out + r * C + c) = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
+// ---- operand image of the weights for the chain kernel ------------------------------------------------------------
+// K-major, 128B-swizzled B operands (row n, element k at n*128 + (((k%64)/8) ^ (n&7))*16 + (k%8)*2 inside a 64-wide K slab):
+//   W2t   [256 rows n = layer-1 unit][K = 64 layer-2 units]      value W2[k][n]          32 KB
+//   W1pt  4 K slabs of [64 rows n = point-feature column][64 k]  value W1[64*slab+k][n]  4 x 8 KB
+//   W3    fp32 [16][64] as it is (dl @ W3 runs on the CUDA cores)                          4 KB
+constexpr int kOffW2t = 0, kOffW1pt = 32768, kOffW3 = 65536, kChainWeightBytes = 65536 + 4096;
+
+__global__ void pack_chain_weights_kernel(const float* __restrict__ W1, const float* __restrict__ W2, const float* __restrict__ W3,
+                                          uint8_t* __restrict__ out) {
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 32768 + 1024; e += gridDim.x * blockDim.x) {
+    if (e < 16384) {            // W2t: 256 x 64
+      const int n = e >> 6, k = e & 63;
+      reinterpret_cast<__nv_bfloat16*>(out + kOffW2t + n * 128 + (((k >> 3) ^ (n & 7)) << 4))[k & 7] = __float2bfloat16_rn(W2[k * kN1 + n]);
+    } else if (e < 32768) {     // W1pt: 4 slabs x 64 x 64
+      const int i = e - 16384, slab = i >> 12, n = (i >> 6) & 63, k = i & 63;
+      reinterpret_cast<__nv_bfloat16*>(out + kOffW1pt + slab * 8192 + n * 128 + (((k >> 3) ^ (n & 7)) << 4))[k & 7] =
+          __float2bfloat16_rn(W1[(slab * 64 + k) * kK1 + n]);
+    } else {
+      reinterpret_cast<float*>(out + kOffW3)[e - 32768] = W3[e - 32768];
     }
   }
-  // lanes l and l + kTx, l + 2 kTx, ... of a warp hold the same columns: butterfly over them, then one shared-memory
-  // atomic per warp and column, one global atomic per block and column
-  __shared__ float s_sum[C];
-  for (int c = threadIdx.x; c < C; c += 256) s_sum[c] = 0.f;
-  __syncthreads();
+}
+
+// ---- dW3 += dl^T @ h2, db3 += column sums of dl (CUDA cores: 2 k FLOP per point) -----------------------------------
+constexpr int kW3Chunk = 64;
+__global__ void __launch_bounds__(256)
+dw3_db3_kernel(const float* __restrict__ dl, const uint16_t* __restrict__ h2, int64_t N, float* __restrict__ dW3, float* __restrict__ db3) {
+  __shared__ float s_dl[kW3Chunk][kC + 1];
+  __shared__ __align__(16) float s_h2[kW3Chunk][kN2 + 4];
+  const int t = threadIdx.x, c = t >> 4, j0 = (t & 15) * 4;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f}, bsum = 0.f;
+  for (int64_t p0 = (int64_t)blockIdx.x * kW3Chunk; p0 < N; p0 += (int64_t)gridDim.x * kW3Chunk) {
+    __syncthreads();
+    for (int i = t; i < kW3Chunk * kC; i += 256) {
+      const int64_t r = p0 + i / kC;
+      s_dl[i / kC][i % kC] = r < N ? __ldg(dl + r * kC + i % kC) : 0.f;
+    }
+    for (int i = t; i < kW3Chunk * (kN2 / 2); i += 256) {
+      const int p = i / (kN2 / 2), w = i % (kN2 / 2);
+      const int64_t r = p0 + p;
+      const uint32_t v = r < N ? __ldg(reinterpret_cast<const uint32_t*>(h2 + r * kN2) + w) : 0u;
+      s_h2[p][2 * w] = bf_lo(v);
+      s_h2[p][2 * w + 1] = bf_hi(v);
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int p = 0; p < kW3Chunk; ++p) {
+      const float a = s_dl[p][c];
+      const float4 h = *reinterpret_cast<const float4*>(&s_h2[p][j0]);
+      acc[0] = fmaf(a, h.x, acc[0]); acc[1] = fmaf(a, h.y, acc[1]); acc[2] = fmaf(a, h.z, acc[2]); acc[3] = fmaf(a, h.w, acc[3]);
+    }
+    if (t < kC)
+      for (int p = 0; p < kW3Chunk; ++p) bsum += s_dl[p][t];
+  }
 #pragma unroll
-  for (int j = 0; j < kJ; ++j)
+  for (int e = 0; e < 4; ++e) atomicAdd(dW3 + c * kN2 + j0 + e, acc[e]);
+  if (t < kC) atomicAdd(db3 + t, bsum);
+}
+
+// =====================================================================================================================
+// dgrad_chain_kernel: per 128-point tile   dh2 = (dl @ W3) * (h2 > 0)   dh1 = (dh2 @ W2) * (h1 > 0)   dx_pt = dh1 @ W1[:, :64]
+// One CTA per SM (cta_group::1), persistent over tiles, 12 warps:
+//   warps 0-3   epilogue, one tile row per thread (TMEM lane): acc1 -> ReLU mask from the h1 tile in shared memory -> bf16
+//               dh1 written over h1 in place (the 128B-swizzled K-major slabs are the A operand of the next product);
+//               accx -> dx_pt (fp32) to HBM
+//   warps 4-7   dh2 of the NEXT tile on the CUDA cores, one row per thread: dl (16 fp32) @ W3 (fp32, shared memory), mask
+//               from h2, bf16 into the dh2 slab (double buffered)
+//   warp  8     TMEM allocation and tcgen05.mma issue: dh2 @ W2 (N = 256, K = 64), dh1 @ W1[:, :64] (N = 64, K = 256)
+//   warp  9     TMA: the tile's h1 rows as four [128 x 64] slabs (zero fill beyond N)
+//   warps 10-11 copy dh2 / dh1 from the slabs to HBM (coalesced; the weight-gradient kernel reads them) and accumulate
+//               the bias gradients db2 / db1 (column sums) in registers
+// =====================================================================================================================
+namespace chain {
+constexpr int kThreads = 384;
+constexpr int kOffH1 = kChainWeightBytes;           // 69632, 1024-aligned
+constexpr int kOffDh2 = kOffH1 + 4 * 16384;         // 135168
+constexpr int kOffBar = kOffDh2 + 2 * 16384;        // 167936
+constexpr int kOffTmem = kOffBar + 16 * 8;
+constexpr int kSmemBytes = kOffTmem + 16;
+static_assert(kOffH1 % 1024 == 0 && kOffDh2 % 1024 == 0, "slab alignment");
+enum { kH1Full = 0, kH1Free = 1, kDh2Full = 2, kDh2Free = 4, kAcc1Full = 6, kAcc1Free = 7, kDh1Full = 8, kAccxFull = 9, kAccxFree = 10, kNumBars = 11 };
+
+struct Params {
+  const float* dl;          // [N,16] fp32
+  const uint16_t* h2;       // [N,64] bf16
+  const uint8_t* weights;   // pack_chain_weights_kernel image
+  uint16_t* dh2_out;        // [N,64] bf16
+  uint16_t* dh1_out;        // [N,256] bf16
+  float* dx_pt;             // [N,64] fp32 or NULL
+  float* db1;               // [256] +=
+  float* db2;               // [64] +=
+  int64_t N;
+  int n_tiles;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const uint32_t sbase = ptx::smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  auto bar = [&](int i) { return sbase + kOffBar + 8 * i; };
+  const int n_iters = p.n_tiles > (int)blockIdx.x ? (p.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bar(kH1Full), 1);
+    ptx::mbar_init(bar(kH1Free), 3);
+    for (int b = 0; b < 2; ++b) { ptx::mbar_init(bar(kDh2Full + b), 4); ptx::mbar_init(bar(kDh2Free + b), 2); }
+    ptx::mbar_init(bar(kAcc1Full), 1);
+    ptx::mbar_init(bar(kAcc1Free), 4);
+    ptx::mbar_init(bar(kDh1Full), 4);
+    ptx::mbar_init(bar(kAccxFull), 1);
+    ptx::mbar_init(bar(kAccxFree), 4);
+    ptx::fence_mbar_init();
+    ptx::tma_prefetch_desc(&tm_h1);
+  }
+  {  // weights: global image -> shared memory (generic proxy), then visible to the tensor core's async-proxy reads
+    const uint4* src = reinterpret_cast<const uint4*>(p.weights);
+    uint4* dst = reinterpret_cast<uint4*>(smem);
+    for (int i = threadIdx.x; i < kChainWeightBytes / 16; i += kThreads) dst[i] = __ldg(src + i);
+    ptx::fence_proxy_async_smem();
+  }
+  if (warp == 8) {
+    ptx::tmem_alloc_1cta(sbase + kOffTmem, 512);
+    ptx::tmem_relinquish_1cta();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmem);
+
+  if (warp < 4) {
+    // ------------------------------------------------ epilogue -------------------------------------------------------
+    const int r = threadIdx.x;
+    const uint32_t tl = tmem + (((uint32_t)warp * 32u) << 16);
+    const uint32_t sw = (uint32_t)r & 7u;
+    for (int it = 0; it < n_iters; ++it) {
+      const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128 + r;
+      wait_bar(bar(kAcc1Full), it & 1);
+      wait_bar(bar(kH1Full), it & 1);
+      ptx::tc_fence_after();
+      uint32_t va[16], vb[16];
+      ptx::tmem_ld16(tl, va);
+#pragma unroll
+      for (int c = 0; c < 16; c += 2) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t(&v)[16] = half ? vb : va;
+          ptx::tmem_wait_ld();
+          if (half == 0) ptx::tmem_ld16(tl + (c + 1) * 16, vb);
+          else if (c + 2 < 16) ptx::tmem_ld16(tl + (c + 2) * 16, va);
+          const int cc = c + half;
+          const uint32_t slab = sbase + kOffH1 + (uint32_t)(cc >> 2) * 16384u + (uint32_t)r * 128u;
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            const uint32_t q = (uint32_t)(cc & 3) * 2u + k;
+            const uint32_t addr = slab + ((q ^ sw) << 4);
+            const uint4 h = ptx::lds128(addr);
+            ptx::sts128(addr, pack2(__uint_as_float(v[8 * k]), __uint_as_float(v[8 * k + 1])) & relu_mask2(h.x),
+                        pack2(__uint_as_float(v[8 * k + 2]), __uint_as_float(v[8 * k + 3])) & relu_mask2(h.y),
+                        pack2(__uint_as_float(v[8 * k + 4]), __uint_as_float(v[8 * k + 5])) & relu_mask2(h.z),
+                        pack2(__uint_as_float(v[8 * k + 6]), __uint_as_float(v[8 * k + 7])) & relu_mask2(h.w));
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        ptx::mbar_arrive_local(bar(kAcc1Free));
+        ptx::mbar_arrive_local(bar(kDh1Full));
+      }
+      __syncwarp();
+      // dx_pt
+      wait_bar(bar(kAccxFull), it & 1);
+      ptx::tc_fence_after();
+      uint32_t x0[16], x1[16];
+      uint4* dst = reinterpret_cast<uint4*>(p.dx_pt + (row < p.N ? row : 0) * kCp);
+      const bool store = p.dx_pt != nullptr && row < p.N;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        ptx::tmem_ld16(tl + 256 + half * 32, x0);
+        ptx::tmem_ld16(tl + 272 + half * 32, x1);
+        ptx::tmem_wait_ld();
+        if (half == 1) {   // the accumulator is in registers: the next tile's product may overwrite it
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive_local(bar(kAccxFree));
+          __syncwarp();
+        }
+        if (store) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            dst[half * 8 + k] = make_uint4(x0[4 * k], x0[4 * k + 1], x0[4 * k + 2], x0[4 * k + 3]);
+            dst[half * 8 + 4 + k] = make_uint4(x1[4 * k], x1[4 * k + 1], x1[4 * k + 2], x1[4 * k + 3]);
+          }
+        }
+      }
+    }
+  } else if (warp < 8) {
+    // ------------------------------------------------ dh2 producers --------------------------------------------------
+    const int i = threadIdx.x - 128;
+    const uint32_t sw = (uint32_t)i & 7u;
+    const uint32_t w3 = sbase + kOffW3;
+    for (int it = 0; it < n_iters; ++it) {
+      const int b = it & 1;
+      const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128 + i;
+      float d[kC];
+      const bool live = row < p.N;
+      const uint4* hh = reinterpret_cast<const uint4*>(p.h2 + (live ? row : 0) * kN2);
+      const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+      if (live) {
+        const float4* g = reinterpret_cast<const float4*>(p.dl + row * kC);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const float4 a = __ldg(g + k); d[4 * k] = a.x; d[4 * k + 1] = a.y; d[4 * k + 2] = a.z; d[4 * k + 3] = a.w; }
+      } else {
+#pragma unroll
+        for (int k = 0; k < kC; ++k) d[k] = 0.f;
+      }
+      uint4 hcur = live ? __ldg(hh) : zero4;
+      if (it >= 2) wait_bar(bar(kDh2Free + b), ((it >> 1) - 1) & 1);
+      const uint32_t slab = sbase + kOffDh2 + (uint32_t)b * 16384u + (uint32_t)i * 128u;
+#pragma unroll 1
+      for (int q = 0; q < 8; ++q) {   // eight output columns at a time: sum over the 16 classes; the next h2 chunk in flight
+        const uint4 hnext = (live && q < 7) ? __ldg(hh + q + 1) : zero4;
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+        for (int c = 0; c < kC; ++c) {
+          const float4 wa = ptx::lds128_ro(w3 + (uint32_t)(c * kN2 + q * 8) * 4u), wb = ptx::lds128_ro(w3 + (uint32_t)(c * kN2 + q * 8 + 4) * 4u);
+          acc[0] = fmaf(d[c], wa.x, acc[0]); acc[1] = fmaf(d[c], wa.y, acc[1]); acc[2] = fmaf(d[c], wa.z, acc[2]); acc[3] = fmaf(d[c], wa.w, acc[3]);
+          acc[4] = fmaf(d[c], wb.x, acc[4]); acc[5] = fmaf(d[c], wb.y, acc[5]); acc[6] = fmaf(d[c], wb.z, acc[6]); acc[7] = fmaf(d[c], wb.w, acc[7]);
+        }
+        ptx::sts128(slab + (((uint32_t)q ^ sw) << 4), pack2(acc[0], acc[1]) & relu_mask2(hcur.x), pack2(acc[2], acc[3]) & relu_mask2(hcur.y),
+                    pack2(acc[4], acc[5]) & relu_mask2(hcur.z), pack2(acc[6], acc[7]) & relu_mask2(hcur.w));
+        hcur = hnext;
+      }
+      ptx::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Full + b));
+      __syncwarp();
+    }
+  } else if (warp == 8) {
+    // ------------------------------------------------ MMA issue ------------------------------------------------------
+    if (lane == 0) {
+      constexpr uint32_t kI1 = ptx::idesc_bf16(128, kN1), kIx = ptx::idesc_bf16(128, kCp);
+      for (int it = 0; it < n_iters; ++it) {
+        const int b = it & 1;
+        wait_bar(bar(kDh2Full + b), (it >> 1) & 1);
+        if (it >= 1) wait_bar(bar(kAcc1Free), (it - 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          ptx::umma_ss_1cta(tmem, ptx::smem_desc_sw128(sbase + kOffDh2 + b * 16384 + kk * 32), ptx::smem_desc_sw128(sbase + kOffW2t + kk * 32),
+                            kI1, kk != 0);
+        ptx::umma_commit_1cta(bar(kAcc1Full));
+        ptx::umma_commit_1cta(bar(kDh2Free + b));
+        wait_bar(bar(kDh1Full), it & 1);
+        if (it >= 1) wait_bar(bar(kAccxFree), (it - 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            ptx::umma_ss_1cta(tmem + 256, ptx::smem_desc_sw128(sbase + kOffH1 + s * 16384 + kk * 32),
+                              ptx::smem_desc_sw128(sbase + kOffW1pt + s * 8192 + kk * 32), kIx, (s | kk) != 0);
+        ptx::umma_commit_1cta(bar(kAccxFull));
+        ptx::umma_commit_1cta(bar(kH1Free));
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // ------------------------------------------------ TMA: h1 tiles --------------------------------------------------
+    if (lane == 0) {
+      for (int it = 0; it < n_iters; ++it) {
+        const int tile = (int)blockIdx.x + it * (int)gridDim.x;
+        if (it >= 1) wait_bar(bar(kH1Free), (it - 1) & 1);
+        ptx::mbar_expect_tx(bar(kH1Full), 4 * 16384);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) ptx::tma_load_2d(sbase + kOffH1 + s * 16384, &tm_h1, 64 * s, tile * 128, bar(kH1Full));
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------ copy-out + bias sums -------------------------------------------
+    const int h = warp - 10, q = lane & 7, rg = lane >> 3;
+    float s1[2][8], s2[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s1[0][e] = s1[1][e] = s2[e] = 0.f;
+    auto drain = [&](uint32_t slab, uint16_t* out, int ld, int col0, int64_t row0, float (&acc)[8]) {
+#pragma unroll 4
+      for (int itr = 0; itr < 32; ++itr) {
+        const int r = itr * 4 + rg;
+        const uint4 v = ptx::lds128(slab + (uint32_t)r * 128u + ((((uint32_t)q) ^ ((uint32_t)r & 7u)) << 4));
+        acc[0] += bf_lo(v.x); acc[1] += bf_hi(v.x); acc[2] += bf_lo(v.y); acc[3] += bf_hi(v.y);
+        acc[4] += bf_lo(v.z); acc[5] += bf_hi(v.z); acc[6] += bf_lo(v.w); acc[7] += bf_hi(v.w);
+        if (row0 + r < p.N) *reinterpret_cast<uint4*>(out + (row0 + r) * ld + col0 + q * 8) = v;
+      }
+    };
+    for (int it = 0; it < n_iters; ++it) {
+      const int b = it & 1;
+      const int64_t row0 = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128;
+      if (h == 0) {
+        wait_bar(bar(kDh2Full + b), (it >> 1) & 1);
+        drain(sbase + kOffDh2 + b * 16384, p.dh2_out, kN2, 0, row0, s2);
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Free + b));
+        __syncwarp();
+      }
+      wait_bar(bar(kDh1Full), it & 1);
+      drain(sbase + kOffH1 + (2 * h) * 16384, p.dh1_out, kN1, (2 * h) * 64, row0, s1[0]);
+      drain(sbase + kOffH1 + (2 * h + 1) * 16384, p.dh1_out, kN1, (2 * h + 1) * 64, row0, s1[1]);
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_local(bar(kH1Free));
+      __syncwarp();
+    }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      float v = acc[j][e];
 #pragma unroll
-      for (int o = 16; o >= kTx; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if ((threadIdx.x & 31) < kTx) atomicAdd(&s_sum[(tx + j * kTx) * 8 + e], v);
+      for (int k = 0; k < 2; ++k) {
+        s1[k][e] += __shfl_xor_sync(0xffffffffu, s1[k][e], 8);
+        s1[k][e] += __shfl_xor_sync(0xffffffffu, s1[k][e], 16);
+      }
+      s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], 8);
+      s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], 16);
     }
+    if (rg == 0 && n_iters > 0) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        atomicAdd(p.db1 + (2 * h) * 64 + q * 8 + e, s1[0][e]);
+        atomicAdd(p.db1 + (2 * h + 1) * 64 + q * 8 + e, s1[1][e]);
+        if (h == 0) atomicAdd(p.db2 + q * 8 + e, s2[e]);
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += 256) atomicAdd(db + c, s_sum[c]);
+  if (warp == 8) ptx::tmem_dealloc_1cta(tmem, 512);
+}
+}  // namespace chain
+
+// =====================================================================================================================
+// wgrad_kernel: dW1 = dh1^T @ X and dW2^T = h1^T @ dh2 with the points as the K dimension.
+// A stage is 64 points: every operand slab is [64 points x 64 features] bf16 = 8 KB, delivered by one TMA box load into
+// the 128B-swizzled layout, which for a [k = point][m/n = feature] tile IS the canonical MN-major UMMA atom
+// (cute/atom/mma_traits_sm100.hpp: Swizzle<3,4,3> o ((T,8,m),(8,k)):((1,T,LBO),(8T,SBO)) with LBO = slab size, SBO = 1024).
+// Rows beyond N are zero-filled by TMA and contribute nothing.
+//   flavour A (CTAs [0, n_a)):      slabs dh1 x4, X[:, 0:256] x4           8 slabs / stage, 3 stages
+//       TMEM [0,256) = dW1[0:128, 0:256]      [256,512) = dW1[128:256, 0:256]
+//   flavour B (CTAs [n_a, grid)):   slabs dh1 x4, X[:, 256:448] x3, h1 x4, dh2 x1     12 slabs / stage, 2 stages
+//       TMEM [0,192) = dW1[0:128, 256:448]    [192,384) = dW1[128:256, 256:448]
+//            [384,448) = dW2^T[0:128, :]      [448,512) = dW2^T[128:256, :]
+// Warp 0 issues the TMA loads, warp 1 the MMAs; at the end warps 2-5 move the accumulators TMEM -> shared memory
+// (transposed, 32 x 32 blocks) -> the CTA's fp32 partial [128][512] with coalesced stores.
+// =====================================================================================================================
+namespace wg {
+constexpr int kKP = 64;                 // points per stage
+constexpr int kSlab = kKP * 128;        // 8192
+constexpr int kThreads = 192;
+constexpr int kRing = 24 * kSlab;       // 196608: 3 stages x 8 slabs or 2 stages x 12 slabs
+constexpr int kOffBar = kRing;
+constexpr int kOffTmem = kOffBar + 16 * 8;
+constexpr int kSmemBytes = kOffTmem + 16;
+constexpr int kPartialFloats = 128 * 512;
+
+struct Params {
+  float* partials;     // [grid][128][512]
+  int64_t N;
+  int n_stages;        // ceil(N / 64)
+  int n_a;             // CTAs of flavour A
+};
+
+template <bool kB>
+__device__ __forceinline__ void run(const CUtensorMap& tm_dh1, const CUtensorMap& tm_x, const CUtensorMap& tm_h1, const CUtensorMap& tm_dh2,
+                                    const Params& p, uint8_t* smem, uint32_t sbase, uint32_t tmem, int warp, int lane) {
+  constexpr int kStages = kB ? 2 : 3, kSlabs = kB ? 12 : 8;
+  constexpr uint32_t kStageBytes = kSlabs * kSlab;
+  auto bar = [&](int i) { return sbase + kOffBar + 8 * i; };   // [0,kStages) full, [4,4+kStages) empty, 8 done
+  const int first = kB ? (int)blockIdx.x - p.n_a : (int)blockIdx.x;
+  const int stride = kB ? (int)gridDim.x - p.n_a : p.n_a;
+  const int n_my = p.n_stages > first ? (p.n_stages - first + stride - 1) / stride : 0;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < n_my; ++i) {
+        const int st = i % kStages, row0 = (first + i * stride) * kKP;
+        if (i >= kStages) wait_bar(bar(4 + st), ((i / kStages) - 1) & 1);
+        ptx::mbar_expect_tx(bar(st), kStageBytes);
+        const uint32_t base = sbase + st * kStageBytes;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) ptx::tma_load_2d(base + s * kSlab, &tm_dh1, 64 * s, row0, bar(st));
+        if (!kB) {
+#pragma unroll
+          for (int s = 0; s < 4; ++s) ptx::tma_load_2d(base + (4 + s) * kSlab, &tm_x, 64 * s, row0, bar(st));
+        } else {
+#pragma unroll
+          for (int s = 0; s < 3; ++s) ptx::tma_load_2d(base + (4 + s) * kSlab, &tm_x, 256 + 64 * s, row0, bar(st));
+#pragma unroll
+          for (int s = 0; s < 4; ++s) ptx::tma_load_2d(base + (7 + s) * kSlab, &tm_h1, 64 * s, row0, bar(st));
+          ptx::tma_load_2d(base + 11 * kSlab, &tm_dh2, 0, row0, bar(st));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t kMN = ptx::kIdescAMajorMN | ptx::kIdescBMajorMN;
+      constexpr uint32_t kI256 = ptx::idesc_bf16(128, 256) | kMN, kI192 = ptx::idesc_bf16(128, 192) | kMN, kI64 = ptx::idesc_bf16(128, 64) | kMN;
+      for (int i = 0; i < n_my; ++i) {
+        const int st = i % kStages;
+        wait_bar(bar(st), (i / kStages) & 1);
+        ptx::tc_fence_after();
+        const uint32_t base = sbase + st * kStageBytes;
+#pragma unroll
+        for (int kk = 0; kk < kKP / 16; ++kk) {
+          const uint32_t koff = kk * 2048;   // 16 k-rows of 128 bytes
+          const uint32_t acc = (i | kk) != 0;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint64_t a = ptx::smem_desc_sw128_ex(base + (2 * h) * kSlab + koff, kSlab, 1024);
+            if (!kB) {
+              ptx::umma_ss_1cta(tmem + h * 256, a, ptx::smem_desc_sw128_ex(base + 4 * kSlab + koff, kSlab, 1024), kI256, acc);
+            } else {
+              ptx::umma_ss_1cta(tmem + h * 192, a, ptx::smem_desc_sw128_ex(base + 4 * kSlab + koff, kSlab, 1024), kI192, acc);
+              ptx::umma_ss_1cta(tmem + 384 + h * 64, ptx::smem_desc_sw128_ex(base + (7 + 2 * h) * kSlab + koff, kSlab, 1024),
+                                ptx::smem_desc_sw128_ex(base + 11 * kSlab + koff, kSlab, 1024), kI64, acc);
+            }
+          }
+        }
+        ptx::umma_commit_1cta(bar(4 + st));
+      }
+      ptx::umma_commit_1cta(bar(8));
+    }
+    __syncwarp();
+  } else {
+    // epilogue: warp w owns TMEM lanes 32*(w & 3); columns in blocks of 32 through a padded [32][33] transpose buffer
+    wait_bar(bar(8), 0);
+    ptx::tc_fence_after();
+    const int qd = warp & 3;
+    float* buf = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 33);   // the ring is idle once `done` completed
+    float* out = p.partials + (size_t)blockIdx.x * kPartialFloats + (size_t)(qd * 32) * 512;
+    const uint32_t tl = tmem + (((uint32_t)qd * 32u) << 16);
+    for (int c0 = 0; c0 < 512; c0 += 32) {
+      uint32_t va[16], vb[16];
+      if (n_my > 0) {
+        ptx::tmem_ld16(tl + c0, va);
+        ptx::tmem_ld16(tl + c0 + 16, vb);
+        ptx::tmem_wait_ld();
+      } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) va[k] = vb[k] = 0u;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < 16; ++k) { buf[lane * 33 + k] = __uint_as_float(va[k]); buf[lane * 33 + 16 + k] = __uint_as_float(vb[k]); }
+      __syncwarp();
+#pragma unroll 8
+      for (int r = 0; r < 32; ++r) out[(size_t)r * 512 + c0 + lane] = buf[r * 33 + lane];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_kernel(const __grid_constant__ CUtensorMap tm_dh1, const __grid_constant__ CUtensorMap tm_x,
+             const __grid_constant__ CUtensorMap tm_h1, const __grid_constant__ CUtensorMap tm_dh2, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const uint32_t sbase = ptx::smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 9; ++i) ptx::mbar_init(sbase + kOffBar + 8 * i, 1);
+    ptx::fence_mbar_init();
+    ptx::tma_prefetch_desc(&tm_dh1);
+    ptx::tma_prefetch_desc(&tm_x);
+    ptx::tma_prefetch_desc(&tm_h1);
+    ptx::tma_prefetch_desc(&tm_dh2);
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc_1cta(sbase + kOffTmem, 512);
+    ptx::tmem_relinquish_1cta();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmem);
+  if ((int)blockIdx.x < p.n_a) run<false>(tm_dh1, tm_x, tm_h1, tm_dh2, p, smem, sbase, tmem, warp, lane);
+  else run<true>(tm_dh1, tm_x, tm_h1, tm_dh2, p, smem, sbase, tmem, warp, lane);
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc_1cta(tmem, 512);
+}
+
+// dW1[f][x] += sum over the flavour-A partials (x < 256) or flavour-B partials (x >= 256); dW2[g][f] += flavour-B partials.
+// One thread per output element, partials added in CTA order (deterministic).
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ partials, int n_a, int n_cta, float* __restrict__ dW1, float* __restrict__ dW2) {
+  const int e = blockIdx.x * 256 + threadIdx.x;
+  if (e < kN1 * kK1) {
+    const int f = e / kK1, x = e % kK1;
+    const bool a = x < 256;
+    const float* src = partials + (size_t)(a ? 0 : n_a) * kPartialFloats + (size_t)(f & 127) * 512 + (a ? (f >> 7) * 256 + x : (f >> 7) * 192 + (x - 256));
+    const int n = a ? n_a : n_cta - n_a;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int i = 0;
+    for (; i + 4 <= n; i += 4) {
+      s0 += src[(size_t)i * kPartialFloats];
+      s1 += src[(size_t)(i + 1) * kPartialFloats];
+      s2 += src[(size_t)(i + 2) * kPartialFloats];
+      s3 += src[(size_t)(i + 3) * kPartialFloats];
+    }
+    for (; i < n; ++i) s0 += src[(size_t)i * kPartialFloats];
+    dW1[e] += (s0 + s1) + (s2 + s3);
+  } else if (e < kN1 * kK1 + kN1 * kN2) {
+    const int i2 = e - kN1 * kK1, f = i2 / kN2, g = i2 % kN2;
+    const float* src = partials + (size_t)n_a * kPartialFloats + (size_t)(f & 127) * 512 + 384 + (f >> 7) * 64 + g;
+    float s = 0.f;
+    for (int i = 0; i < n_cta - n_a; ++i) s += src[(size_t)i * kPartialFloats];
+    dW2[g * kN1 + f] += s;
+  }
+}
+}  // namespace wg
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point query: libtdssf.so does not link libcuda
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 row-major [rows, cols] matrix, box = [box_rows x 64 columns] (128 bytes wide), 128B swizzle, zero fill out of bounds
+static bool make_map(CUtensorMap* m, const void* base, int64_t rows, int cols, int box_rows) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 struct Work {
-  uint16_t *X, *dl, *dh2, *dh1, *W1, *W2, *W3;
+  uint16_t *X, *dh2, *dh1;
+  uint8_t* chain_w;
+  float* partials;
 };
 static size_t al(size_t b) { return (b + 255) & ~(size_t)255; }
-static size_t carve(int64_t N, char* base, Work* w) {
+static size_t carve(int64_t N, int n_cta, char* base, Work* w) {
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += al(bytes); return p; };
   uint16_t* X = (uint16_t*)take((size_t)N * kK1 * 2);
-  uint16_t* dl = (uint16_t*)take((size_t)N * kC * 2);
   uint16_t* dh2 = (uint16_t*)take((size_t)N * kN2 * 2);
   uint16_t* dh1 = (uint16_t*)take((size_t)N * kN1 * 2);
-  uint16_t* W1 = (uint16_t*)take((size_t)kN1 * kK1 * 2);
-  uint16_t* W2 = (uint16_t*)take((size_t)kN2 * kN1 * 2);
-  uint16_t* W3 = (uint16_t*)take((size_t)kC * kN2 * 2);
-  if (w) *w = Work{X, dl, dh2, dh1, W1, W2, W3};
+  uint8_t* cw = (uint8_t*)take(kChainWeightBytes);
+  float* partials = (float*)take((size_t)n_cta * wg::kPartialFloats * 4);
+  if (w) *w = Work{X, dh2, dh1, cw, partials};
   return off;
+}
+// the weight-gradient grid: one CTA per SM, at most one per stage of 64 points and at least one of each flavour
+static int wgrad_ctas(int64_t N) { return (int)std::max<int64_t>(2, std::min<int64_t>(num_sms(), 2 * ceil_div(N, wg::kKP))); }
+
+template <typename K>
+static int set_smem(K kern, int bytes, bool (&done)[kMaxDevices]) {
+  const int dev = current_device();
+  if (!done[dev]) {
+    TDSSF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done[dev] = true;
+  }
+  return TDSSF_OK;
 }
 
 }  // namespace bwd
 }  // namespace tdssf
 
 extern "C" size_t tdssf_mlp_bwd_tc_workspace_bytes(int64_t N) {
-  return tdssf::bwd::carve(N < 0 ? 0 : N, nullptr, nullptr) + 256;
+  if (N < 0) N = 0;
+  return tdssf::bwd::carve(N, tdssf::bwd::wgrad_ctas(N), nullptr, nullptr) + 256;
 }
 
 extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* x_bf16, const void* h1_bf16, const void* h2_bf16,
@@ -206,7 +668,7 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
   TDSSF_REQUIRE(w_host->W1 && w_host->W2 && w_host->W3, "tdssf_mlp_bwd_tc: NULL weight pointer");
   TDSSF_REQUIRE(g_host->dW1 && g_host->db1 && g_host->dW2 && g_host->db2 && g_host->dW3 && g_host->db3,
                 "tdssf_mlp_bwd_tc: NULL gradient pointer");
-  TDSSF_REQUIRE(N >= 0 && N < (1ll << 31), "tdssf_mlp_bwd_tc: N out of range");
+  TDSSF_REQUIRE(N >= 0 && N < (1ll << 31) - 256, "tdssf_mlp_bwd_tc: N out of range");
   if (N == 0) return TDSSF_OK;
   TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)x_bf16 | (uintptr_t)h1_bf16 | (uintptr_t)h2_bf16 | (uintptr_t)dlogits |
                   (uintptr_t)dx_pt) & 15) == 0, "tdssf_mlp_bwd_tc: pointers must be 16-byte aligned");
@@ -214,47 +676,54 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
                 "tdssf_mlp_bwd_tc: 256-byte aligned workspace of %zu bytes needed, got %zu",
                 tdssf_mlp_bwd_tc_workspace_bytes(N), workspace_bytes);
   if (int rc = tdssf_check_device()) return rc;
-  cublasHandle_t h = handle_for_current_device();
-  if (!h) {
-    set_error("tdssf_mlp_bwd_tc: cuBLAS (libcublas.so.12) could not be loaded");
-    return TDSSF_ENOSUP;
-  }
   cudaStream_t s = (cudaStream_t)stream;
-  if (cublas().set_stream(h, s) != CUBLAS_STATUS_SUCCESS) {
-    set_error("tdssf_mlp_bwd_tc: cublasSetStream failed");
-    return TDSSF_ECUDA;
-  }
+  const int n_cta = wgrad_ctas(N);
   Work w;
-  carve(N, reinterpret_cast<char*>(workspace), &w);
+  carve(N, n_cta, reinterpret_cast<char*>(workspace), &w);
   const unsigned blocks = (unsigned)num_sms() * 8;
-  // operands in bf16
-  cvt3_bf16_kernel<<<blocks, 256, 0, s>>>(w_host->W1, reinterpret_cast<uint4*>(w.W1), (int64_t)kN1 * kK1 / 8,
-                                          w_host->W2, reinterpret_cast<uint4*>(w.W2), (int64_t)kN2 * kN1 / 8,
-                                          w_host->W3, reinterpret_cast<uint4*>(w.W3), (int64_t)kC * kN2 / 8);
+
+  pack_chain_weights_kernel<<<64, 256, 0, s>>>(w_host->W1, w_host->W2, w_host->W3, w.chain_w);
+  TDSSF_LAUNCH_CHECK();
   const void* X = x_bf16;
   if (!X) {
     concat_bf16_kernel<<<blocks, 256, 0, s>>>(x_pt, x_img, reinterpret_cast<uint4*>(w.X), N);
+    TDSSF_LAUNCH_CHECK();
     X = w.X;
   }
-  mask_cvt_colsum_kernel<kC, float><<<blocks, 256, 0, s>>>(dlogits, nullptr, w.dl, g_host->db3, N);
+  CUtensorMap tm_h1_128, tm_dh1, tm_x, tm_h1, tm_dh2;
+  if (!make_map(&tm_h1_128, h1_bf16, N, kN1, 128) || !make_map(&tm_dh1, w.dh1, N, kN1, wg::kKP) || !make_map(&tm_x, X, N, kK1, wg::kKP) ||
+      !make_map(&tm_h1, h1_bf16, N, kN1, wg::kKP) || !make_map(&tm_dh2, w.dh2, N, kN2, wg::kKP)) {
+    set_error("tdssf_mlp_bwd_tc: cuTensorMapEncodeTiled failed (driver entry point unavailable or bad tensor geometry)");
+    return TDSSF_ECUDA;
+  }
+
+  // 1. data-gradient chain (writes dh2, dh1, dx_pt; accumulates db2, db1)
+  {
+    static bool done[kMaxDevices] = {};
+    if (int rc = set_smem(chain::dgrad_chain_kernel, chain::kSmemBytes + 1024, done)) return rc;
+    chain::Params p = {};
+    p.dl = dlogits; p.h2 = reinterpret_cast<const uint16_t*>(h2_bf16); p.weights = w.chain_w;
+    p.dh2_out = w.dh2; p.dh1_out = w.dh1; p.dx_pt = dx_pt; p.db1 = g_host->db1; p.db2 = g_host->db2;
+    p.N = N; p.n_tiles = (int)ceil_div(N, 128);
+    const int grid = std::min(num_sms(), p.n_tiles);
+    chain::dgrad_chain_kernel<<<grid, chain::kThreads, chain::kSmemBytes + 1024, s>>>(tm_h1_128, p);
+    TDSSF_LAUNCH_CHECK();
+  }
+  // 2. dW3, db3 on the CUDA cores
+  dw3_db3_kernel<<<(unsigned)std::min<int64_t>(num_sms() * 2, ceil_div(N, kW3Chunk)), 256, 0, s>>>(
+      dlogits, reinterpret_cast<const uint16_t*>(h2_bf16), N, g_host->dW3, g_host->db3);
   TDSSF_LAUNCH_CHECK();
-  const int n = (int)N;
-  auto ok = [&](cublasStatus_t st, const char* what) {
-    if (st == CUBLAS_STATUS_SUCCESS) return true;
-    set_error("tdssf_mlp_bwd_tc: cublasGemmEx(%s) failed with status %d", what, (int)st);
-    return false;
-  };
-  // data gradients
-  // (the two hidden-layer data gradients leave cuBLAS as bf16, directly in the buffers the mask kernels finish in place)
-  if (!ok(gemm_rm(h, false, false, n, kN2, kC, 1.f, w.dl, kC, w.W3, kN2, 0.f, w.dh2, kN2, true), "dH2")) return TDSSF_ECUDA;
-  mask_cvt_colsum_kernel<kN2, uint16_t><<<blocks, 256, 0, s>>>(w.dh2, reinterpret_cast<const uint16_t*>(h2_bf16), w.dh2, g_host->db2, N);
-  if (!ok(gemm_rm(h, false, false, n, kN1, kN2, 1.f, w.dh2, kN2, w.W2, kN1, 0.f, w.dh1, kN1, true), "dH1")) return TDSSF_ECUDA;
-  mask_cvt_colsum_kernel<kN1, uint16_t><<<blocks, 256, 0, s>>>(w.dh1, reinterpret_cast<const uint16_t*>(h1_bf16), w.dh1, g_host->db1, N);
-  TDSSF_LAUNCH_CHECK();
-  if (dx_pt && !ok(gemm_rm(h, false, false, n, kCp, kN1, 1.f, w.dh1, kN1, w.W1, kK1, 0.f, dx_pt, kCp), "dx_pt")) return TDSSF_ECUDA;
-  // weight gradients, accumulated into the caller's fp32 buffers
-  if (!ok(gemm_rm(h, true, false, kC, kN2, n, 1.f, w.dl, kC, h2_bf16, kN2, 1.f, g_host->dW3, kN2), "dW3")) return TDSSF_ECUDA;
-  if (!ok(gemm_rm(h, true, false, kN2, kN1, n, 1.f, w.dh2, kN2, h1_bf16, kN1, 1.f, g_host->dW2, kN1), "dW2")) return TDSSF_ECUDA;
-  if (!ok(gemm_rm(h, true, false, kN1, kK1, n, 1.f, w.dh1, kN1, X, kK1, 1.f, g_host->dW1, kK1), "dW1")) return TDSSF_ECUDA;
+  // 3. dW1, dW2: per-CTA partials in TMEM, then one ordered reduction into the caller's buffers
+  {
+    static bool done[kMaxDevices] = {};
+    if (int rc = set_smem(wg::wgrad_kernel, wg::kSmemBytes + 1024, done)) return rc;
+    wg::Params p = {};
+    p.partials = w.partials; p.N = N; p.n_stages = (int)ceil_div(N, wg::kKP);
+    p.n_a = std::max(1, std::min(n_cta - 1, (n_cta * 2 + 2) / 5));   // bytes per stage 8 : 12 slabs -> CTAs 2 : 3
+    wg::wgrad_kernel<<<n_cta, wg::kThreads, wg::kSmemBytes + 1024, s>>>(tm_dh1, tm_x, tm_h1, tm_dh2, p);
+    TDSSF_LAUNCH_CHECK();
+    wg::wgrad_reduce_kernel<<<(kN1 * kK1 + kN1 * kN2 + 255) / 256, 256, 0, s>>>(w.partials, p.n_a, n_cta, g_host->dW1, g_host->dW2);
+    TDSSF_LAUNCH_CHECK();
+  }
   return TDSSF_OK;
 }

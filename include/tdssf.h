@@ -183,8 +183,10 @@ TDSSF_API int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N,
  * replaces  the autograd of FeatureFusionModel.mlp   utils/fusion_model.py:144-150,203-204 (utils/train.py:91)
  * The input rows come either as x_bf16 [N,448] (saved by tdssf_fusion_fwd) or, when x_bf16 is NULL, as fp32 x_pt / x_img.
  * Accumulates (+=) dW*, db* into the caller's fp32 buffers (zeroed by the caller) and writes dx_pt [N,64] (may be NULL).
- * The six products are plain GEMMs and run in cuBLAS (bf16 operands, fp32 accumulate), loaded at first use; the
- * conversions, ReLU masks and bias-gradient sums are kernels of this library.  TDSSF_ENOSUP if cuBLAS cannot be loaded.
+ * Every product is a hand-written kernel of this library (csrc/mlp_bwd_tc.cu; no vendor GEMM library): the data-gradient
+ * chain dl@W3 -> mask -> @W2 -> mask -> @W1[:, :64] per 128-point tile with tcgen05.mma (the ReLU masks, bias sums and bf16
+ * copies in its epilogues), and the weight gradients dW1 / dW2 with the points as the K dimension of tcgen05.mma on MN-major
+ * operands delivered by TMA, accumulated per CTA in TMEM and reduced in a fixed order (deterministic); dW3 / db3 on the CUDA cores.
  * workspace: tdssf_mlp_bwd_tc_workspace_bytes(N), 256-byte aligned. */
 TDSSF_API size_t tdssf_mlp_bwd_tc_workspace_bytes(int64_t N);
 TDSSF_API int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* x_bf16, const void* h1_bf16, const void* h2_bf16,

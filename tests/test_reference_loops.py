@@ -29,6 +29,10 @@ def loops():
     return ref_loader.load_loops(dropin_eval)
 
 
+def _host(x):
+    return np.asarray(x.detach().cpu() if torch.is_tensor(x) else x, dtype=np.float64)
+
+
 def _setup(n_batches=4, B=2, V=3000, seed=70):
     from utils.fusion_model import FeatureFusionModel
     from utils.losses import CELSLoss
@@ -73,8 +77,8 @@ def test_reference_test_model_and_sample_match_dropin_loops(loops, tmp_path, cap
     want = loops.test.test_model(loaders, enc, pcd, model, crit, "cuda")
     got = dropin_loops.test_model(loaders, enc, pcd, model, crit, "cuda")
     assert set(got) == set(want)
-    for k in want:
-        assert np.allclose(np.asarray(got[k], np.float64), np.asarray(want[k], np.float64), rtol=1e-6, atol=1e-9), k
+    for k in want:   # the reference returns overall_acc as a CUDA tensor (total_corrects.double() / total_points)
+        assert np.allclose(_host(got[k]), _host(want[k]), rtol=1e-6, atol=1e-9), k
 
     config = {"test_params": {"checkpoint_path": str(tmp_path)}}
     s_want = loops.test.test_sample(config, loaders, enc, pcd, model, crit, "cuda")
@@ -84,5 +88,5 @@ def test_reference_test_model_and_sample_match_dropin_loops(loops, tmp_path, cap
     assert torch.equal(s_got["predictions"], s_want["predictions"]) and torch.equal(s_got["labels"], s_want["labels"])
     assert np.array_equal(s_got["points"], s_want["points"])
     for k in ("loss", "overall_acc", "mean_iou", "mean_per_class_acc", "precision", "recall", "f1"):
-        assert np.allclose(float(s_got[k]), float(s_want[k]), rtol=1e-6, atol=1e-9), k
+        assert np.allclose(_host(s_got[k]), _host(s_want[k]), rtol=1e-6, atol=1e-9), k
     assert "EVALUATION METRICS" in capsys.readouterr().out
