@@ -14,7 +14,7 @@
 //                        the TMEM epilogues (the h1 tile arrives by TMA and is overwritten in place by dh1, which is the
 //                        A operand of the next product), bias sums and the bf16 copies of dh2 / dh1 for the weight
 //                        gradients written from shared memory by two helper warps.  Bound: HBM (about 223 MB per 4 sweeps).
-//   dw3_db3_kernel       dW3 (16 x 64, 0.3 GFLOP) and db3 on the CUDA cores.
+//   dw3_db3_kernel       dW3 (16 x 64, 0.3 GFLOP) and db3 on the CUDA cores, as per-block partials.
 //   wgrad_kernel         dW1 and dW2 with the points as the K dimension: both operands are the row-major [points, features]
 //                        matrices as they lie in HBM, i.e. MN-major UMMA operands, delivered by TMA into 128B-swizzled
 //                        slabs; every CTA accumulates its share of the points into TMEM (512 columns, all used) and writes
@@ -40,12 +40,6 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 }
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
-// bf16 > 0  <=>  sign clear and not zero, for the two halves of a packed word: 0xffff / 0 per half
-__device__ __forceinline__ uint32_t relu_mask2(uint32_t h) {
-  const uint32_t lo = h & 0xffffu, hi = h >> 16;
-  return ((lo != 0u && !(lo & 0x8000u)) ? 0x0000ffffu : 0u) | ((hi != 0u && !(hi & 0x8000u)) ? 0xffff0000u : 0u);
-}
-
 __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity) {
   if (ptx::mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
@@ -90,64 +84,88 @@ __global__ void pack_chain_weights_kernel(const float* __restrict__ W1, const fl
   }
 }
 
-// ---- dW3 += dl^T @ h2, db3 += column sums of dl (CUDA cores: 2 k FLOP per point) -----------------------------------
-constexpr int kW3Chunk = 64;
-__global__ void __launch_bounds__(256)
-dw3_db3_kernel(const float* __restrict__ dl, const uint16_t* __restrict__ h2, int64_t N, float* __restrict__ dW3, float* __restrict__ db3) {
-  __shared__ float s_dl[kW3Chunk][kC + 1];
-  __shared__ __align__(16) float s_h2[kW3Chunk][kN2 + 4];
-  const int t = threadIdx.x, c = t >> 4, j0 = (t & 15) * 4;
-  float acc[4] = {0.f, 0.f, 0.f, 0.f}, bsum = 0.f;
-  for (int64_t p0 = (int64_t)blockIdx.x * kW3Chunk; p0 < N; p0 += (int64_t)gridDim.x * kW3Chunk) {
-    __syncthreads();
-    for (int i = t; i < kW3Chunk * kC; i += 256) {
-      const int64_t r = p0 + i / kC;
-      s_dl[i / kC][i % kC] = r < N ? __ldg(dl + r * kC + i % kC) : 0.f;
+// ---- dW3 = dl^T @ h2 and db3 = column sums of dl on the CUDA cores (2 k FLOP per point: a streaming reduction) ------
+// A warp takes 32 consecutive rows at a time: lane l loads dl row l (64 bytes) and, for every row of the group, the h2
+// columns 2l, 2l+1 (32 coalesced 128-byte requests), all issued before the first use; the 16 dl values of row j then
+// reach every lane by shuffles, and lane l keeps the 16 x 2 sums of its columns in registers.  Per block the eight
+// warps are added through shared memory into one partial [1024 + 16]; wgrad_reduce_kernel adds the partials in block
+// order (deterministic, no atomics).
+constexpr int kW3Out = kC * kN2 + kC;   // 1040
+__global__ void __launch_bounds__(256, 2)
+dw3_db3_kernel(const float* __restrict__ dl, const uint16_t* __restrict__ h2, int64_t N, float* __restrict__ partial) {
+  __shared__ float s_acc[8][kW3Out];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc[kC][2], bs[kC];
+#pragma unroll
+  for (int c = 0; c < kC; ++c) acc[c][0] = acc[c][1] = bs[c] = 0.f;
+  const int64_t n_groups = (N + 31) / 32, W = (int64_t)gridDim.x * 8;
+  for (int64_t g = (int64_t)blockIdx.x * 8 + warp; g < n_groups; g += W) {
+    const int64_t r0 = g * 32;
+    const bool mine = r0 + lane < N;
+    const float4* dp = reinterpret_cast<const float4*>(dl + (mine ? r0 + lane : 0) * kC);
+    float4 d4[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) d4[k] = mine ? __ldg(dp + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t hv[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) hv[j] = r0 + j < N ? __ldg(reinterpret_cast<const uint32_t*>(h2 + (r0 + j) * kN2) + lane) : 0u;
+    const float d[kC] = {d4[0].x, d4[0].y, d4[0].z, d4[0].w, d4[1].x, d4[1].y, d4[1].z, d4[1].w,
+                         d4[2].x, d4[2].y, d4[2].z, d4[2].w, d4[3].x, d4[3].y, d4[3].z, d4[3].w};
+#pragma unroll
+    for (int c = 0; c < kC; ++c) bs[c] += d[c];   // this lane's row; the lanes are added at the end
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float h0 = bf_lo(hv[j]), h1 = bf_hi(hv[j]);
+#pragma unroll
+      for (int c = 0; c < kC; ++c) {
+        const float v = __shfl_sync(0xffffffffu, d[c], j);
+        acc[c][0] = fmaf(v, h0, acc[c][0]);
+        acc[c][1] = fmaf(v, h1, acc[c][1]);
+      }
     }
-    for (int i = t; i < kW3Chunk * (kN2 / 2); i += 256) {
-      const int p = i / (kN2 / 2), w = i % (kN2 / 2);
-      const int64_t r = p0 + p;
-      const uint32_t v = r < N ? __ldg(reinterpret_cast<const uint32_t*>(h2 + r * kN2) + w) : 0u;
-      s_h2[p][2 * w] = bf_lo(v);
-      s_h2[p][2 * w + 1] = bf_hi(v);
-    }
-    __syncthreads();
-#pragma unroll 8
-    for (int p = 0; p < kW3Chunk; ++p) {
-      const float a = s_dl[p][c];
-      const float4 h = *reinterpret_cast<const float4*>(&s_h2[p][j0]);
-      acc[0] = fmaf(a, h.x, acc[0]); acc[1] = fmaf(a, h.y, acc[1]); acc[2] = fmaf(a, h.z, acc[2]); acc[3] = fmaf(a, h.w, acc[3]);
-    }
-    if (t < kC)
-      for (int p = 0; p < kW3Chunk; ++p) bsum += s_dl[p][t];
   }
 #pragma unroll
-  for (int e = 0; e < 4; ++e) atomicAdd(dW3 + c * kN2 + j0 + e, acc[e]);
-  if (t < kC) atomicAdd(db3 + t, bsum);
+  for (int c = 0; c < kC; ++c) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) bs[c] += __shfl_xor_sync(0xffffffffu, bs[c], o);
+    *reinterpret_cast<float2*>(&s_acc[warp][c * kN2 + 2 * lane]) = make_float2(acc[c][0], acc[c][1]);
+    if (lane == 0) s_acc[warp][kC * kN2 + c] = bs[c];
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < kW3Out; e += 256) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += s_acc[w][e];
+    partial[(size_t)blockIdx.x * kW3Out + e] = v;
+  }
 }
 
 // =====================================================================================================================
 // dgrad_chain_kernel: per 128-point tile   dh2 = (dl @ W3) * (h2 > 0)   dh1 = (dh2 @ W2) * (h1 > 0)   dx_pt = dh1 @ W1[:, :64]
-// One CTA per SM (cta_group::1), persistent over tiles, 12 warps:
+// One CTA per SM (cta_group::1), persistent over tiles, 14 working warps:
 //   warps 0-3   epilogue, one tile row per thread (TMEM lane): acc1 -> ReLU mask from the h1 tile in shared memory -> bf16
 //               dh1 written over h1 in place (the 128B-swizzled K-major slabs are the A operand of the next product);
 //               accx -> dx_pt (fp32) to HBM
 //   warps 4-7   dh2 of the NEXT tile on the CUDA cores, one row per thread: dl (16 fp32) @ W3 (fp32, shared memory), mask
-//               from h2, bf16 into the dh2 slab (double buffered)
+//               from h2, bf16 into the dh2 slab; the row's dl and first h2 chunks are fetched one tile ahead
 //   warp  8     TMEM allocation and tcgen05.mma issue: dh2 @ W2 (N = 256, K = 64), dh1 @ W1[:, :64] (N = 64, K = 256)
-//   warp  9     TMA: the tile's h1 rows as four [128 x 64] slabs (zero fill beyond N)
-//   warps 10-11 copy dh2 / dh1 from the slabs to HBM (coalesced; the weight-gradient kernel reads them) and accumulate
-//               the bias gradients db2 / db1 (column sums) in registers
+//   warp  9     TMA: the tile's h1 rows as four [128 x 64] slabs (zero fill beyond N), two tiles in flight; every slab has
+//               its own full / free barriers, so it is refilled as soon as its K step and its copy-out are done
+//   warps 10-13 copy dh1 (one slab each) and dh2 (warp 10) from the slabs to HBM with coalesced stores (the weight-
+//               gradient kernel reads them) and accumulate the bias gradients db1 / db2 (column sums) in registers
 // =====================================================================================================================
 namespace chain {
-constexpr int kThreads = 384;
-constexpr int kOffH1 = kChainWeightBytes;           // 69632, 1024-aligned
-constexpr int kOffDh2 = kOffH1 + 4 * 16384;         // 135168
-constexpr int kOffBar = kOffDh2 + 2 * 16384;        // 167936
-constexpr int kOffTmem = kOffBar + 16 * 8;
+constexpr int kThreads = 512;
+constexpr int kOffH1 = kChainWeightBytes;           // 69632, 1024-aligned; two buffers of 4 x 16 KB
+constexpr int kOffDh2 = kOffH1 + 2 * 65536;         // 200704
+constexpr int kOffBar = kOffDh2 + 16384;            // 217088
+constexpr int kOffTmem = kOffBar + 32 * 8;
 constexpr int kSmemBytes = kOffTmem + 16;
 static_assert(kOffH1 % 1024 == 0 && kOffDh2 % 1024 == 0, "slab alignment");
-enum { kH1Full = 0, kH1Free = 1, kDh2Full = 2, kDh2Free = 4, kAcc1Full = 6, kAcc1Free = 7, kDh1Full = 8, kAccxFull = 9, kAccxFree = 10, kNumBars = 11 };
+static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget");
+// the h1 / dh1 tile is handed over slab by slab (64 columns): [buffer][slab] full / free barriers, one dh1-full barrier per slab
+enum { kH1Full = 0, kH1Free = 8, kDh2Full = 16, kDh2Free = 17, kAcc1Full = 18, kAcc1Free = 19, kDh1Full = 20, kAccxFull = 24, kAccxFree = 25,
+       kWFull = 26, kNumBars = 27 };
 
 struct Params {
   const float* dl;          // [N,16] fp32
@@ -162,6 +180,11 @@ struct Params {
   int n_tiles;
 };
 
+// 0xffff per half of a packed bf16 pair that is > 0 (the ReLU mask of the saved activation)
+__device__ __forceinline__ uint32_t relu_mask2(uint32_t h) {
+  return __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&h), __floats2bfloat162_rn(0.f, 0.f));
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -170,24 +193,20 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   auto bar = [&](int i) { return sbase + kOffBar + 8 * i; };
   const int n_iters = p.n_tiles > (int)blockIdx.x ? (p.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  auto tile_of = [&](int it) { return (int64_t)blockIdx.x + (int64_t)it * gridDim.x; };
 
   if (threadIdx.x == 0) {
-    ptx::mbar_init(bar(kH1Full), 1);
-    ptx::mbar_init(bar(kH1Free), 3);
-    for (int b = 0; b < 2; ++b) { ptx::mbar_init(bar(kDh2Full + b), 4); ptx::mbar_init(bar(kDh2Free + b), 2); }
+    for (int b = 0; b < 8; ++b) { ptx::mbar_init(bar(kH1Full + b), 1); ptx::mbar_init(bar(kH1Free + b), 2); }   // commit + copy-out warp
+    ptx::mbar_init(bar(kDh2Full), 4);
+    ptx::mbar_init(bar(kDh2Free), 5);   // the product's commit + the four copy-out warps
+    ptx::mbar_init(bar(kWFull), 1);
     ptx::mbar_init(bar(kAcc1Full), 1);
     ptx::mbar_init(bar(kAcc1Free), 4);
-    ptx::mbar_init(bar(kDh1Full), 4);
+    for (int b = 0; b < 4; ++b) ptx::mbar_init(bar(kDh1Full + b), 4);
     ptx::mbar_init(bar(kAccxFull), 1);
     ptx::mbar_init(bar(kAccxFree), 4);
     ptx::fence_mbar_init();
     ptx::tma_prefetch_desc(&tm_h1);
-  }
-  {  // weights: global image -> shared memory (generic proxy), then visible to the tensor core's async-proxy reads
-    const uint4* src = reinterpret_cast<const uint4*>(p.weights);
-    uint4* dst = reinterpret_cast<uint4*>(smem);
-    for (int i = threadIdx.x; i < kChainWeightBytes / 16; i += kThreads) dst[i] = __ldg(src + i);
-    ptx::fence_proxy_async_smem();
   }
   if (warp == 8) {
     ptx::tmem_alloc_1cta(sbase + kOffTmem, 512);
@@ -197,6 +216,11 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmem);
+  if (threadIdx.x == 0) {   // the weight image lands (TMA bulk copies) while the first tile's inputs are fetched
+    ptx::mbar_expect_tx(bar(kWFull), kChainWeightBytes);
+    for (int off = 0; off < kChainWeightBytes; off += 16384)
+      ptx::bulk_g2s(sbase + off, p.weights + off, min(16384, kChainWeightBytes - off), bar(kWFull));
+  }
 
   if (warp < 4) {
     // ------------------------------------------------ epilogue -------------------------------------------------------
@@ -204,9 +228,9 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
     const uint32_t tl = tmem + (((uint32_t)warp * 32u) << 16);
     const uint32_t sw = (uint32_t)r & 7u;
     for (int it = 0; it < n_iters; ++it) {
-      const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128 + r;
+      const int hb = it & 1;
+      const int64_t row = tile_of(it) * 128 + r;
       wait_bar(bar(kAcc1Full), it & 1);
-      wait_bar(bar(kH1Full), it & 1);
       ptx::tc_fence_after();
       uint32_t va[16], vb[16];
       ptx::tmem_ld16(tl, va);
@@ -219,7 +243,11 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
           if (half == 0) ptx::tmem_ld16(tl + (c + 1) * 16, vb);
           else if (c + 2 < 16) ptx::tmem_ld16(tl + (c + 2) * 16, va);
           const int cc = c + half;
-          const uint32_t slab = sbase + kOffH1 + (uint32_t)(cc >> 2) * 16384u + (uint32_t)r * 128u;
+          if ((cc & 3) == 0) wait_bar(bar(kH1Full + hb * 4 + (cc >> 2)), (it >> 1) & 1);   // this slab of h1 has landed
+          const uint32_t slab = sbase + kOffH1 + (uint32_t)hb * 65536u + (uint32_t)(cc >> 2) * 16384u + (uint32_t)r * 128u;
+#ifdef TDSSF_CH_NOE1   // (timing experiment: TMEM loads only)
+          if (p.N < 0)
+#endif
 #pragma unroll
           for (int k = 0; k < 2; ++k) {
             const uint32_t q = (uint32_t)(cc & 3) * 2u + k;
@@ -230,16 +258,18 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
                         pack2(__uint_as_float(v[8 * k + 4]), __uint_as_float(v[8 * k + 5])) & relu_mask2(h.z),
                         pack2(__uint_as_float(v[8 * k + 6]), __uint_as_float(v[8 * k + 7])) & relu_mask2(h.w));
           }
+          if ((cc & 3) == 3) {   // a dh1 slab is complete: the next product's K step and the copy-out warp may read it
+            if (cc == 15) ptx::tc_fence_before();
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (cc == 15) ptx::mbar_arrive_local(bar(kAcc1Free));
+              ptx::mbar_arrive_local(bar(kDh1Full + (cc >> 2)));
+            }
+            __syncwarp();
+          }
         }
       }
-      ptx::tc_fence_before();
-      ptx::fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        ptx::mbar_arrive_local(bar(kAcc1Free));
-        ptx::mbar_arrive_local(bar(kDh1Full));
-      }
-      __syncwarp();
       // dx_pt
       wait_bar(bar(kAccxFull), it & 1);
       ptx::tc_fence_after();
@@ -257,13 +287,16 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
           if (lane == 0) ptx::mbar_arrive_local(bar(kAccxFree));
           __syncwarp();
         }
-        if (store) {
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            dst[half * 8 + k] = make_uint4(x0[4 * k], x0[4 * k + 1], x0[4 * k + 2], x0[4 * k + 3]);
-            dst[half * 8 + 4 + k] = make_uint4(x1[4 * k], x1[4 * k + 1], x1[4 * k + 2], x1[4 * k + 3]);
-          }
+#ifndef TDSSF_CH_NODX   // (timing experiment: no dx_pt stores)
+        if (store) {   // a row per thread: 32-byte stores, every lane in its own line
+          ptx::stg256(dst + half * 8, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], x0[6], x0[7]);
+          ptx::stg256(dst + half * 8 + 2, x0[8], x0[9], x0[10], x0[11], x0[12], x0[13], x0[14], x0[15]);
+          ptx::stg256(dst + half * 8 + 4, x1[0], x1[1], x1[2], x1[3], x1[4], x1[5], x1[6], x1[7]);
+          ptx::stg256(dst + half * 8 + 6, x1[8], x1[9], x1[10], x1[11], x1[12], x1[13], x1[14], x1[15]);
         }
+#else
+        (void)store; (void)dst;
+#endif
       }
     }
   } else if (warp < 8) {
@@ -271,71 +304,97 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
     const int i = threadIdx.x - 128;
     const uint32_t sw = (uint32_t)i & 7u;
     const uint32_t w3 = sbase + kOffW3;
+    const uint32_t slab = sbase + kOffDh2 + (uint32_t)i * 128u;
+    // The whole row is computed into registers BEFORE the wait for the slab (the previous tile's product and copy-out
+    // still read it), so that what sits between "slab free" and "slab full" is eight 16-byte stores.
+    ptx::u32x8 dn[2], hn[4];   // the next tile's dl row and h2 row, in flight while this tile is computed
+    auto prefetch = [&](int it) {
+      const int64_t row = tile_of(it) * 128 + i;
+      const bool live = it < n_iters && row < p.N;
+      const char* g = reinterpret_cast<const char*>(p.dl + (live ? row : 0) * kC);
+      const char* hh = reinterpret_cast<const char*>(p.h2 + (live ? row : 0) * kN2);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) dn[k] = ptx::ldg256(g + 32 * k);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) hn[k] = ptx::ldg256(hh + 32 * k);
+      if (!live) {   // rows beyond N: zero gradient and zero mask
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { dn[0].v[e] = dn[1].v[e] = 0u; hn[0].v[e] = hn[1].v[e] = hn[2].v[e] = hn[3].v[e] = 0u; }
+      }
+    };
+    prefetch(0);
+    wait_bar(bar(kWFull), 0);   // W3
     for (int it = 0; it < n_iters; ++it) {
-      const int b = it & 1;
-      const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128 + i;
       float d[kC];
-      const bool live = row < p.N;
-      const uint4* hh = reinterpret_cast<const uint4*>(p.h2 + (live ? row : 0) * kN2);
-      const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
-      if (live) {
-        const float4* g = reinterpret_cast<const float4*>(p.dl + row * kC);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { const float4 a = __ldg(g + k); d[4 * k] = a.x; d[4 * k + 1] = a.y; d[4 * k + 2] = a.z; d[4 * k + 3] = a.w; }
-      } else {
+      for (int c = 0; c < kC; ++c) d[c] = __uint_as_float(dn[c >> 3].v[c & 7]);
+      uint32_t res[32];
 #pragma unroll
-        for (int k = 0; k < kC; ++k) d[k] = 0.f;
-      }
-      uint4 hcur = live ? __ldg(hh) : zero4;
-      if (it >= 2) wait_bar(bar(kDh2Free + b), ((it >> 1) - 1) & 1);
-      const uint32_t slab = sbase + kOffDh2 + (uint32_t)b * 16384u + (uint32_t)i * 128u;
+      for (int k = 0; k < 32; ++k) res[k] = 0u;
 #pragma unroll 1
-      for (int q = 0; q < 8; ++q) {   // eight output columns at a time: sum over the 16 classes; the next h2 chunk in flight
-        const uint4 hnext = (live && q < 7) ? __ldg(hh + q + 1) : zero4;
-        float acc[8];
+      for (int qq = 0; qq < 4; ++qq) {   // sixteen output columns per pass (a real loop: the 64 W3 loads of a pass stay
+                                         // next to their use); the results shift through `res` so that every index is static
+        uint32_t fresh[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        for (int half = 0; half < 2; ++half) {
+          float acc[8];
 #pragma unroll
-        for (int c = 0; c < kC; ++c) {
-          const float4 wa = ptx::lds128_ro(w3 + (uint32_t)(c * kN2 + q * 8) * 4u), wb = ptx::lds128_ro(w3 + (uint32_t)(c * kN2 + q * 8 + 4) * 4u);
-          acc[0] = fmaf(d[c], wa.x, acc[0]); acc[1] = fmaf(d[c], wa.y, acc[1]); acc[2] = fmaf(d[c], wa.z, acc[2]); acc[3] = fmaf(d[c], wa.w, acc[3]);
-          acc[4] = fmaf(d[c], wb.x, acc[4]); acc[5] = fmaf(d[c], wb.y, acc[5]); acc[6] = fmaf(d[c], wb.z, acc[6]); acc[7] = fmaf(d[c], wb.w, acc[7]);
+          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#ifndef TDSSF_CH_NOPROD   // (timing experiment: no dl @ W3)
+          const uint32_t wq = w3 + (uint32_t)(qq * 16 + half * 8) * 4u;
+#pragma unroll
+          for (int c = 0; c < kC; ++c) {
+            const float4 wa = ptx::lds128_ro(wq + (uint32_t)(c * kN2) * 4u), wb = ptx::lds128_ro(wq + (uint32_t)(c * kN2 + 4) * 4u);
+            acc[0] = fmaf(d[c], wa.x, acc[0]); acc[1] = fmaf(d[c], wa.y, acc[1]); acc[2] = fmaf(d[c], wa.z, acc[2]); acc[3] = fmaf(d[c], wa.w, acc[3]);
+            acc[4] = fmaf(d[c], wb.x, acc[4]); acc[5] = fmaf(d[c], wb.y, acc[5]); acc[6] = fmaf(d[c], wb.z, acc[6]); acc[7] = fmaf(d[c], wb.w, acc[7]);
+          }
+#endif
+#pragma unroll
+          for (int k = 0; k < 4; ++k) fresh[4 * half + k] = pack2(acc[2 * k], acc[2 * k + 1]) & relu_mask2(hn[0].v[4 * half + k]);
         }
-        ptx::sts128(slab + (((uint32_t)q ^ sw) << 4), pack2(acc[0], acc[1]) & relu_mask2(hcur.x), pack2(acc[2], acc[3]) & relu_mask2(hcur.y),
-                    pack2(acc[4], acc[5]) & relu_mask2(hcur.z), pack2(acc[6], acc[7]) & relu_mask2(hcur.w));
-        hcur = hnext;
+#pragma unroll
+        for (int k = 0; k < 24; ++k) res[k] = res[k + 8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) res[24 + k] = fresh[k];
+        hn[0] = hn[1]; hn[1] = hn[2]; hn[2] = hn[3];
       }
+      prefetch(it + 1);
+      if (it >= 1) wait_bar(bar(kDh2Free), (it - 1) & 1);
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        ptx::sts128(slab + (((uint32_t)q ^ sw) << 4), res[4 * q], res[4 * q + 1], res[4 * q + 2], res[4 * q + 3]);
       ptx::fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Full + b));
+      if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Full));
       __syncwarp();
     }
   } else if (warp == 8) {
     // ------------------------------------------------ MMA issue ------------------------------------------------------
     if (lane == 0) {
       constexpr uint32_t kI1 = ptx::idesc_bf16(128, kN1), kIx = ptx::idesc_bf16(128, kCp);
+      wait_bar(bar(kWFull), 0);
       for (int it = 0; it < n_iters; ++it) {
-        const int b = it & 1;
-        wait_bar(bar(kDh2Full + b), (it >> 1) & 1);
+        const int hb = it & 1;
+        wait_bar(bar(kDh2Full), it & 1);
         if (it >= 1) wait_bar(bar(kAcc1Free), (it - 1) & 1);
         ptx::tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          ptx::umma_ss_1cta(tmem, ptx::smem_desc_sw128(sbase + kOffDh2 + b * 16384 + kk * 32), ptx::smem_desc_sw128(sbase + kOffW2t + kk * 32),
-                            kI1, kk != 0);
+          ptx::umma_ss_1cta(tmem, ptx::smem_desc_sw128(sbase + kOffDh2 + kk * 32), ptx::smem_desc_sw128(sbase + kOffW2t + kk * 32), kI1, kk != 0);
         ptx::umma_commit_1cta(bar(kAcc1Full));
-        ptx::umma_commit_1cta(bar(kDh2Free + b));
-        wait_bar(bar(kDh1Full), it & 1);
+        ptx::umma_commit_1cta(bar(kDh2Free));
         if (it >= 1) wait_bar(bar(kAccxFree), (it - 1) & 1);
-        ptx::tc_fence_after();
 #pragma unroll
-        for (int s = 0; s < 4; ++s)
+        for (int s = 0; s < 4; ++s) {
+          wait_bar(bar(kDh1Full + s), it & 1);
+          ptx::tc_fence_after();
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            ptx::umma_ss_1cta(tmem + 256, ptx::smem_desc_sw128(sbase + kOffH1 + s * 16384 + kk * 32),
+            ptx::umma_ss_1cta(tmem + 256, ptx::smem_desc_sw128(sbase + kOffH1 + hb * 65536 + s * 16384 + kk * 32),
                               ptx::smem_desc_sw128(sbase + kOffW1pt + s * 8192 + kk * 32), kIx, (s | kk) != 0);
+          ptx::umma_commit_1cta(bar(kH1Free + hb * 4 + s));
+        }
         ptx::umma_commit_1cta(bar(kAccxFull));
-        ptx::umma_commit_1cta(bar(kH1Free));
       }
     }
     __syncwarp();
@@ -343,24 +402,29 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
     // ------------------------------------------------ TMA: h1 tiles --------------------------------------------------
     if (lane == 0) {
       for (int it = 0; it < n_iters; ++it) {
-        const int tile = (int)blockIdx.x + it * (int)gridDim.x;
-        if (it >= 1) wait_bar(bar(kH1Free), (it - 1) & 1);
-        ptx::mbar_expect_tx(bar(kH1Full), 4 * 16384);
+        const int hb = it & 1;
 #pragma unroll
-        for (int s = 0; s < 4; ++s) ptx::tma_load_2d(sbase + kOffH1 + s * 16384, &tm_h1, 64 * s, tile * 128, bar(kH1Full));
+        for (int s = 0; s < 4; ++s) {
+          if (it >= 2) wait_bar(bar(kH1Free + hb * 4 + s), ((it >> 1) - 1) & 1);
+          ptx::mbar_expect_tx(bar(kH1Full + hb * 4 + s), 16384);
+          ptx::tma_load_2d(sbase + kOffH1 + hb * 65536 + s * 16384, &tm_h1, 64 * s, (int)(tile_of(it) * 128), bar(kH1Full + hb * 4 + s));
+        }
       }
     }
     __syncwarp();
-  } else {
+  } else if (warp < 14) {
     // ------------------------------------------------ copy-out + bias sums -------------------------------------------
     const int h = warp - 10, q = lane & 7, rg = lane >> 3;
-    float s1[2][8], s2[8];
+    float s1[8], s2[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) s1[0][e] = s1[1][e] = s2[e] = 0.f;
-    auto drain = [&](uint32_t slab, uint16_t* out, int ld, int col0, int64_t row0, float (&acc)[8]) {
+    for (int e = 0; e < 8; ++e) s1[e] = s2[e] = 0.f;
+    // rows [r_lo, r_hi) of a [128 x 64] slab: four rows per instruction (eight lanes x 16 bytes each)
+    auto drain = [&](uint32_t slab, uint16_t* out, int ld, int col0, int64_t row0, int r_lo, int r_hi, float (&acc)[8]) {
+#ifdef TDSSF_CH_NODRAIN   // (timing experiment: helpers only run the barrier protocol)
+      if (p.N >= 0) return;
+#endif
 #pragma unroll 4
-      for (int itr = 0; itr < 32; ++itr) {
-        const int r = itr * 4 + rg;
+      for (int r = r_lo + rg; r < r_hi; r += 4) {
         const uint4 v = ptx::lds128(slab + (uint32_t)r * 128u + ((((uint32_t)q) ^ ((uint32_t)r & 7u)) << 4));
         acc[0] += bf_lo(v.x); acc[1] += bf_hi(v.x); acc[2] += bf_lo(v.y); acc[3] += bf_hi(v.y);
         acc[4] += bf_lo(v.z); acc[5] += bf_hi(v.z); acc[6] += bf_lo(v.w); acc[7] += bf_hi(v.w);
@@ -368,38 +432,31 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
       }
     };
     for (int it = 0; it < n_iters; ++it) {
-      const int b = it & 1;
-      const int64_t row0 = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128;
-      if (h == 0) {
-        wait_bar(bar(kDh2Full + b), (it >> 1) & 1);
-        drain(sbase + kOffDh2 + b * 16384, p.dh2_out, kN2, 0, row0, s2);
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Free + b));
-        __syncwarp();
-      }
-      wait_bar(bar(kDh1Full), it & 1);
-      drain(sbase + kOffH1 + (2 * h) * 16384, p.dh1_out, kN1, (2 * h) * 64, row0, s1[0]);
-      drain(sbase + kOffH1 + (2 * h + 1) * 16384, p.dh1_out, kN1, (2 * h + 1) * 64, row0, s1[1]);
+      const int hb = it & 1;
+      const int64_t row0 = tile_of(it) * 128;
+      wait_bar(bar(kDh2Full), it & 1);
+      drain(sbase + kOffDh2, p.dh2_out, kN2, 0, row0, 32 * h, 32 * h + 32, s2);
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_local(bar(kH1Free));
+      if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Free));
+      __syncwarp();
+      wait_bar(bar(kDh1Full + h), it & 1);
+      drain(sbase + kOffH1 + hb * 65536 + h * 16384, p.dh1_out, kN1, h * 64, row0, 0, 128, s1);
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_local(bar(kH1Free + hb * 4 + h));
       __syncwarp();
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        s1[k][e] += __shfl_xor_sync(0xffffffffu, s1[k][e], 8);
-        s1[k][e] += __shfl_xor_sync(0xffffffffu, s1[k][e], 16);
-      }
+      s1[e] += __shfl_xor_sync(0xffffffffu, s1[e], 8);
+      s1[e] += __shfl_xor_sync(0xffffffffu, s1[e], 16);
       s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], 8);
       s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], 16);
     }
     if (rg == 0 && n_iters > 0) {
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        atomicAdd(p.db1 + (2 * h) * 64 + q * 8 + e, s1[0][e]);
-        atomicAdd(p.db1 + (2 * h + 1) * 64 + q * 8 + e, s1[1][e]);
-        if (h == 0) atomicAdd(p.db2 + q * 8 + e, s2[e]);
+        atomicAdd(p.db1 + h * 64 + q * 8 + e, s1[e]);
+        atomicAdd(p.db2 + q * 8 + e, s2[e]);
       }
     }
   }
@@ -421,13 +478,13 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
 //   flavour B (CTAs [n_a, grid)):   slabs dh1 x4, X[:, 256:448] x3, h1 x4, dh2 x1     12 slabs / stage, 2 stages
 //       TMEM [0,192) = dW1[0:128, 256:448]    [192,384) = dW1[128:256, 256:448]
 //            [384,448) = dW2^T[0:128, :]      [448,512) = dW2^T[128:256, :]
-// Warp 0 issues the TMA loads, warp 1 the MMAs; at the end warps 2-5 move the accumulators TMEM -> shared memory
-// (transposed, 32 x 32 blocks) -> the CTA's fp32 partial [128][512] with coalesced stores.
+// Warp 0 issues the TMA loads, warp 1 the MMAs; at the end warps 2-9 move the accumulators TMEM -> shared memory
+// (transposed, 32 x 32 blocks) -> the CTA's fp32 partial [128][512] with coalesced 16-byte stores.
 // =====================================================================================================================
 namespace wg {
 constexpr int kKP = 64;                 // points per stage
 constexpr int kSlab = kKP * 128;        // 8192
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;
 constexpr int kRing = 24 * kSlab;       // 196608: 3 stages x 8 slabs or 2 stages x 12 slabs
 constexpr int kOffBar = kRing;
 constexpr int kOffTmem = kOffBar + 16 * 8;
@@ -488,6 +545,9 @@ __device__ __forceinline__ void run(const CUtensorMap& tm_dh1, const CUtensorMap
           const uint32_t acc = (i | kk) != 0;
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
+#ifdef TDSSF_WG_NOMMA   // (timing experiment: loads only)
+            continue;
+#endif
             const uint64_t a = ptx::smem_desc_sw128_ex(base + (2 * h) * kSlab + koff, kSlab, 1024);
             if (!kB) {
               ptx::umma_ss_1cta(tmem + h * 256, a, ptx::smem_desc_sw128_ex(base + 4 * kSlab + koff, kSlab, 1024), kI256, acc);
@@ -504,14 +564,19 @@ __device__ __forceinline__ void run(const CUtensorMap& tm_dh1, const CUtensorMap
     }
     __syncwarp();
   } else {
-    // epilogue: warp w owns TMEM lanes 32*(w & 3); columns in blocks of 32 through a padded [32][33] transpose buffer
+    // epilogue, eight warps: warp w owns TMEM lanes 32*(w & 3) and the column half (w - 2) >> 2; blocks of 32 columns go
+    // through a [32][36]-float transpose buffer (16-byte accesses on both sides, conflict-free: rows 144 bytes apart) so
+    // that the partial is written with 16-byte stores that cover four full 128-byte rows per instruction
     wait_bar(bar(8), 0);
     ptx::tc_fence_after();
-    const int qd = warp & 3;
-    float* buf = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 33);   // the ring is idle once `done` completed
+    const int qd = warp & 3, ch = (warp - 2) >> 2;
+    float* buf = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 36);   // the ring is idle once `done` completed
     float* out = p.partials + (size_t)blockIdx.x * kPartialFloats + (size_t)(qd * 32) * 512;
     const uint32_t tl = tmem + (((uint32_t)qd * 32u) << 16);
-    for (int c0 = 0; c0 < 512; c0 += 32) {
+#ifdef TDSSF_WG_NOEPI   // (timing experiment: no partial written)
+    if (p.N >= 0) return;
+#endif
+    for (int c0 = ch * 256; c0 < ch * 256 + 256; c0 += 32) {
       uint32_t va[16], vb[16];
       if (n_my > 0) {
         ptx::tmem_ld16(tl + c0, va);
@@ -522,11 +587,18 @@ __device__ __forceinline__ void run(const CUtensorMap& tm_dh1, const CUtensorMap
         for (int k = 0; k < 16; ++k) va[k] = vb[k] = 0u;
       }
       __syncwarp();
+      uint4* mine = reinterpret_cast<uint4*>(buf + lane * 36);
 #pragma unroll
-      for (int k = 0; k < 16; ++k) { buf[lane * 33 + k] = __uint_as_float(va[k]); buf[lane * 33 + 16 + k] = __uint_as_float(vb[k]); }
+      for (int k = 0; k < 4; ++k) {
+        mine[k] = make_uint4(va[4 * k], va[4 * k + 1], va[4 * k + 2], va[4 * k + 3]);
+        mine[4 + k] = make_uint4(vb[4 * k], vb[4 * k + 1], vb[4 * k + 2], vb[4 * k + 3]);
+      }
       __syncwarp();
-#pragma unroll 8
-      for (int r = 0; r < 32; ++r) out[(size_t)r * 512 + c0 + lane] = buf[r * 33 + lane];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int r = 4 * j + (lane >> 3);
+        *reinterpret_cast<uint4*>(out + (size_t)r * 512 + c0 + 4 * (lane & 7)) = *reinterpret_cast<const uint4*>(buf + r * 36 + 4 * (lane & 7));
+      }
     }
   }
 }
@@ -564,7 +636,26 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tm_dh1, const __grid_constant__
 // dW1[f][x] += sum over the flavour-A partials (x < 256) or flavour-B partials (x >= 256); dW2[g][f] += flavour-B partials.
 // One thread per output element, partials added in CTA order (deterministic).
 __global__ void __launch_bounds__(256)
-wgrad_reduce_kernel(const float* __restrict__ partials, int n_a, int n_cta, float* __restrict__ dW1, float* __restrict__ dW2) {
+wgrad_reduce_kernel(const float* __restrict__ partials, int n_a, int n_cta, float* __restrict__ dW1, float* __restrict__ dW2,
+                    const float* __restrict__ partials3, int n3, float* __restrict__ dW3, float* __restrict__ db3) {
+  constexpr int kMainBlocks = (kN1 * kK1 + kN1 * kN2 + 255) / 256;
+  if ((int)blockIdx.x >= kMainBlocks) {
+    // dW3 / db3: 32 outputs per block, eight threads per output walk the dw3_db3_kernel partials, then a shared-memory sum
+    __shared__ float s[8][32];
+    const int o = ((int)blockIdx.x - kMainBlocks) * 32 + (threadIdx.x & 31), k = threadIdx.x >> 5;
+    float v = 0.f;
+    if (o < kW3Out)
+      for (int b = k; b < n3; b += 8) v += partials3[(size_t)b * kW3Out + o];
+    s[k][threadIdx.x & 31] = v;
+    __syncthreads();
+    if (k == 0 && o < kW3Out) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += s[j][threadIdx.x];
+      if (o < kC * kN2) dW3[o] += t; else db3[o - kC * kN2] += t;
+    }
+    return;
+  }
   const int e = blockIdx.x * 256 + threadIdx.x;
   if (e < kN1 * kK1) {
     const int f = e / kK1, x = e % kK1;
@@ -617,13 +708,15 @@ static bool make_map(CUtensorMap* m, const void* base, int64_t rows, int cols, i
   const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+constexpr int kMaxW3Blocks = 1024;
 struct Work {
   uint16_t *X, *dh2, *dh1;
   uint8_t* chain_w;
   float* partials;
+  float* partials3;
 };
 static size_t al(size_t b) { return (b + 255) & ~(size_t)255; }
 static size_t carve(int64_t N, int n_cta, char* base, Work* w) {
@@ -634,7 +727,8 @@ static size_t carve(int64_t N, int n_cta, char* base, Work* w) {
   uint16_t* dh1 = (uint16_t*)take((size_t)N * kN1 * 2);
   uint8_t* cw = (uint8_t*)take(kChainWeightBytes);
   float* partials = (float*)take((size_t)n_cta * wg::kPartialFloats * 4);
-  if (w) *w = Work{X, dh2, dh1, cw, partials};
+  float* partials3 = (float*)take((size_t)kMaxW3Blocks * kW3Out * 4);
+  if (w) *w = Work{X, dh2, dh1, cw, partials, partials3};
   return off;
 }
 // the weight-gradient grid: one CTA per SM, at most one per stage of 64 points and at least one of each flavour
@@ -671,7 +765,7 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
   TDSSF_REQUIRE(N >= 0 && N < (1ll << 31) - 256, "tdssf_mlp_bwd_tc: N out of range");
   if (N == 0) return TDSSF_OK;
   TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)x_bf16 | (uintptr_t)h1_bf16 | (uintptr_t)h2_bf16 | (uintptr_t)dlogits |
-                  (uintptr_t)dx_pt) & 15) == 0, "tdssf_mlp_bwd_tc: pointers must be 16-byte aligned");
+                  (uintptr_t)dx_pt) & 31) == 0, "tdssf_mlp_bwd_tc: pointers must be 32-byte aligned");
   TDSSF_REQUIRE(workspace && ((uintptr_t)workspace & 255) == 0 && workspace_bytes >= tdssf_mlp_bwd_tc_workspace_bytes(N),
                 "tdssf_mlp_bwd_tc: 256-byte aligned workspace of %zu bytes needed, got %zu",
                 tdssf_mlp_bwd_tc_workspace_bytes(N), workspace_bytes);
@@ -710,8 +804,8 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     TDSSF_LAUNCH_CHECK();
   }
   // 2. dW3, db3 on the CUDA cores
-  dw3_db3_kernel<<<(unsigned)std::min<int64_t>(num_sms() * 2, ceil_div(N, kW3Chunk)), 256, 0, s>>>(
-      dlogits, reinterpret_cast<const uint16_t*>(h2_bf16), N, g_host->dW3, g_host->db3);
+  const int n3 = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(num_sms() * 2, kMaxW3Blocks), ceil_div(N, 256)));
+  dw3_db3_kernel<<<n3, 256, 0, s>>>(dlogits, reinterpret_cast<const uint16_t*>(h2_bf16), N, w.partials3);
   TDSSF_LAUNCH_CHECK();
   // 3. dW1, dW2: per-CTA partials in TMEM, then one ordered reduction into the caller's buffers
   {
@@ -722,7 +816,8 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     p.n_a = std::max(1, std::min(n_cta - 1, (n_cta * 2 + 2) / 5));   // bytes per stage 8 : 12 slabs -> CTAs 2 : 3
     wg::wgrad_kernel<<<n_cta, wg::kThreads, wg::kSmemBytes + 1024, s>>>(tm_dh1, tm_x, tm_h1, tm_dh2, p);
     TDSSF_LAUNCH_CHECK();
-    wg::wgrad_reduce_kernel<<<(kN1 * kK1 + kN1 * kN2 + 255) / 256, 256, 0, s>>>(w.partials, p.n_a, n_cta, g_host->dW1, g_host->dW2);
+    wg::wgrad_reduce_kernel<<<(kN1 * kK1 + kN1 * kN2 + 255) / 256 + (kW3Out + 31) / 32, 256, 0, s>>>(
+        w.partials, p.n_a, n_cta, g_host->dW1, g_host->dW2, w.partials3, n3, g_host->dW3, g_host->db3);
     TDSSF_LAUNCH_CHECK();
   }
   return TDSSF_OK;

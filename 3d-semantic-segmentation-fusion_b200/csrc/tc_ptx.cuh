@@ -275,6 +275,21 @@ __device__ __forceinline__ uint64_t lds64(uint32_t addr) {
   return v;
 }
 
+// 256-bit global accesses (sm_100: LDG.E.256 / STG.E.256): half the instructions - and half the L1 wavefront replays -
+// of a row-per-thread access pattern, where every lane touches its own 128-byte line
+struct u32x8 { uint32_t v[8]; };
+__device__ __forceinline__ u32x8 ldg256(const void* p) {
+  u32x8 r;
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg256(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e, uint32_t f, uint32_t g, uint32_t h) {
+  asm volatile("st.global.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h)
+               : "memory");
+}
+
 // register budget of the executing warpgroup (all four warps must execute it)
 template <int kRegs>
 __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs)); }

@@ -187,7 +187,7 @@ TDSSF_API int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N,
  * chain dl@W3 -> mask -> @W2 -> mask -> @W1[:, :64] per 128-point tile with tcgen05.mma (the ReLU masks, bias sums and bf16
  * copies in its epilogues), and the weight gradients dW1 / dW2 with the points as the K dimension of tcgen05.mma on MN-major
  * operands delivered by TMA, accumulated per CTA in TMEM and reduced in a fixed order (deterministic); dW3 / db3 on the CUDA cores.
- * workspace: tdssf_mlp_bwd_tc_workspace_bytes(N), 256-byte aligned. */
+ * All pointers 32-byte aligned (256-bit row accesses).  workspace: tdssf_mlp_bwd_tc_workspace_bytes(N), 256-byte aligned. */
 TDSSF_API size_t tdssf_mlp_bwd_tc_workspace_bytes(int64_t N);
 TDSSF_API int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const void* x_bf16, const void* h1_bf16, const void* h2_bf16,
                      const float* dlogits, int64_t N, const tdssf_mlp_weights* w_host,
