@@ -9,7 +9,7 @@
 //   dx_pt = dh1 @ W1[:, :64]         [N,64]
 //
 // Three launches after the operand packing:
-//   dgrad_chain_kernel   the data-gradient chain per 128-point tile: dl @ W3 on the CUDA cores (K = 16), dh2 @ W2 and
+//   dgrad_chain_kernel   the data-gradient chain per 128-point tile: dl @ W3, dh2 @ W2 and
 //                        dh1 @ W1[:, :64] as tcgen05.mma with the weights resident in shared memory, the ReLU masks in
 //                        the TMEM epilogues (the h1 tile arrives by TMA and is overwritten in place by dh1, which is the
 //                        A operand of the next product), bias sums and the bf16 copies of dh2 / dh1 for the weight
@@ -65,8 +65,9 @@ __global__ void concat_bf16_kernel(const float* __restrict__ x_pt, const float* 
 // K-major, 128B-swizzled B operands (row n, element k at n*128 + (((k%64)/8) ^ (n&7))*16 + (k%8)*2 inside a 64-wide K slab):
 //   W2t   [256 rows n = layer-1 unit][K = 64 layer-2 units]      value W2[k][n]          32 KB
 //   W1pt  4 K slabs of [64 rows n = point-feature column][64 k]  value W1[64*slab+k][n]  4 x 8 KB
-//   W3    fp32 [16][64] as it is (dl @ W3 runs on the CUDA cores)                          4 KB
-constexpr int kOffW2t = 0, kOffW1pt = 32768, kOffW3 = 65536, kChainWeightBytes = 65536 + 4096;
+//   W3t   [64 rows n = layer-2 unit][K = 16 classes], no swizzle: 8-row x 16-byte core matrices, element (n, k) at
+//         (n/8)*256 + (k/8)*128 + (n%8)*16 + (k%8)*2, value W3[k][n]                      2 KB
+constexpr int kOffW2t = 0, kOffW1pt = 32768, kOffW3 = 65536, kChainWeightBytes = 65536 + 2048;
 
 __global__ void pack_chain_weights_kernel(const float* __restrict__ W1, const float* __restrict__ W2, const float* __restrict__ W3,
                                           uint8_t* __restrict__ out) {
@@ -78,8 +79,9 @@ __global__ void pack_chain_weights_kernel(const float* __restrict__ W1, const fl
       const int i = e - 16384, slab = i >> 12, n = (i >> 6) & 63, k = i & 63;
       reinterpret_cast<__nv_bfloat16*>(out + kOffW1pt + slab * 8192 + n * 128 + (((k >> 3) ^ (n & 7)) << 4))[k & 7] =
           __float2bfloat16_rn(W1[(slab * 64 + k) * kK1 + n]);
-    } else {
-      reinterpret_cast<float*>(out + kOffW3)[e - 32768] = W3[e - 32768];
+    } else {                    // W3t: 64 x 16
+      const int i = e - 32768, n = i >> 4, k = i & 15;
+      reinterpret_cast<__nv_bfloat16*>(out + kOffW3 + (n >> 3) * 256 + (k >> 3) * 128 + (n & 7) * 16)[k & 7] = __float2bfloat16_rn(W3[k * kN2 + n]);
     }
   }
 }
@@ -146,26 +148,36 @@ dw3_db3_kernel(const float* __restrict__ dl, const uint16_t* __restrict__ h2, in
 //   warps 0-3   epilogue, one tile row per thread (TMEM lane): acc1 -> ReLU mask from the h1 tile in shared memory -> bf16
 //               dh1 written over h1 in place (the 128B-swizzled K-major slabs are the A operand of the next product);
 //               accx -> dx_pt (fp32) to HBM
-//   warps 4-7   dh2 of the NEXT tile on the CUDA cores, one row per thread: dl (16 fp32) @ W3 (fp32, shared memory), mask
-//               from h2, bf16 into the dh2 slab; the row's dl and first h2 chunks are fetched one tile ahead
-//   warp  8     TMEM allocation and tcgen05.mma issue: dh2 @ W2 (N = 256, K = 64), dh1 @ W1[:, :64] (N = 64, K = 256)
+//   warps 4-7   dh2 of the NEXT tile, one row per thread: dl -> bf16 -> K = 16 A operand (no swizzle) of dl @ W3 on the tensor
+//               core; then its epilogue: mask from h2, bf16 into the dh2 slab; the rows' dl and h2 are fetched one tile ahead
+//   warp  8     TMEM allocation and tcgen05.mma issue: dl @ W3 (N = 64, K = 16), dh2 @ W2 (N = 256, K = 64), dh1 @ W1[:, :64]
+//               (N = 64, K = 256)
 //   warp  9     TMA: the tile's h1 rows as four [128 x 64] slabs (zero fill beyond N), two tiles in flight; every slab has
 //               its own full / free barriers, so it is refilled as soon as its K step and its copy-out are done
 //   warps 10-13 copy dh1 (one slab each) and dh2 (warp 10) from the slabs to HBM with coalesced stores (the weight-
 //               gradient kernel reads them) and accumulate the bias gradients db1 / db2 (column sums) in registers
 // =====================================================================================================================
 namespace chain {
+#ifdef TDSSF_CH_TRACE   // (experiment builds) clock64 of event `ev` of tile `it`, CTA 0 only
+#define CH_TRACE(ev, it)                                                                                   \
+  do {                                                                                                     \
+    if (p.trace && blockIdx.x == 0 && (threadIdx.x & 31) == 0 && (it) < 16) p.trace[(ev) * 16 + (it)] = clock64(); \
+  } while (0)
+#else
+#define CH_TRACE(ev, it)
+#endif
 constexpr int kThreads = 512;
 constexpr int kOffH1 = kChainWeightBytes;           // 69632, 1024-aligned; two buffers of 4 x 16 KB
-constexpr int kOffDh2 = kOffH1 + 2 * 65536;         // 200704
-constexpr int kOffBar = kOffDh2 + 16384;            // 217088
+constexpr int kOffDh2 = kOffH1 + 2 * 65536;         // 198656
+constexpr int kOffDl = kOffDh2 + 16384;             // dl tile as a no-swizzle K-major A operand: 128 rows x 32 bytes = 4 KB
+constexpr int kOffBar = kOffDl + 4096;
 constexpr int kOffTmem = kOffBar + 32 * 8;
 constexpr int kSmemBytes = kOffTmem + 16;
 static_assert(kOffH1 % 1024 == 0 && kOffDh2 % 1024 == 0, "slab alignment");
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget");
 // the h1 / dh1 tile is handed over slab by slab (64 columns): [buffer][slab] full / free barriers, one dh1-full barrier per slab
 enum { kH1Full = 0, kH1Free = 8, kDh2Full = 16, kDh2Free = 17, kAcc1Full = 18, kAcc1Free = 19, kDh1Full = 20, kAccxFull = 24, kAccxFree = 25,
-       kWFull = 26, kNumBars = 27 };
+       kWFull = 26, kDlFull = 27, kAcc2Full = 28, kNumBars = 29 };
 
 struct Params {
   const float* dl;          // [N,16] fp32
@@ -174,10 +186,10 @@ struct Params {
   uint16_t* dh2_out;        // [N,64] bf16
   uint16_t* dh1_out;        // [N,256] bf16
   float* dx_pt;             // [N,64] fp32 or NULL
-  float* db1;               // [256] +=
-  float* db2;               // [64] +=
+  float* bias_partial;      // [grid][320]: this CTA's column sums of dh1 (256) and dh2 (64); summed by wgrad_reduce_kernel
   int64_t N;
   int n_tiles;
+  long long* trace;         // experiment builds only
 };
 
 // 0xffff per half of a packed bf16 pair that is > 0 (the ReLU mask of the saved activation)
@@ -200,6 +212,8 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
     ptx::mbar_init(bar(kDh2Full), 4);
     ptx::mbar_init(bar(kDh2Free), 5);   // the product's commit + the four copy-out warps
     ptx::mbar_init(bar(kWFull), 1);
+    ptx::mbar_init(bar(kDlFull), 4);
+    ptx::mbar_init(bar(kAcc2Full), 1);
     ptx::mbar_init(bar(kAcc1Full), 1);
     ptx::mbar_init(bar(kAcc1Free), 4);
     for (int b = 0; b < 4; ++b) ptx::mbar_init(bar(kDh1Full + b), 4);
@@ -232,28 +246,33 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
       const int64_t row = tile_of(it) * 128 + r;
       wait_bar(bar(kAcc1Full), it & 1);
       ptx::tc_fence_after();
+      if (warp == 0) CH_TRACE(0, it);
       uint32_t va[16], vb[16];
+      uint4 hq[8];   // the row's eight 16-byte chunks of the current h1 slab, loaded in one go when the slab has landed
       ptx::tmem_ld16(tl, va);
 #pragma unroll
       for (int c = 0; c < 16; c += 2) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t(&v)[16] = half ? vb : va;
+          const int cc = c + half;
+          const uint32_t slab = sbase + kOffH1 + (uint32_t)hb * 65536u + (uint32_t)(cc >> 2) * 16384u + (uint32_t)r * 128u;
+          if ((cc & 3) == 0) {
+            wait_bar(bar(kH1Full + hb * 4 + (cc >> 2)), (it >> 1) & 1);   // this slab of h1 has landed
+#pragma unroll
+            for (int q = 0; q < 8; ++q) hq[q] = ptx::lds128(slab + (((uint32_t)q ^ sw) << 4));
+          }
           ptx::tmem_wait_ld();
           if (half == 0) ptx::tmem_ld16(tl + (c + 1) * 16, vb);
           else if (c + 2 < 16) ptx::tmem_ld16(tl + (c + 2) * 16, va);
-          const int cc = c + half;
-          if ((cc & 3) == 0) wait_bar(bar(kH1Full + hb * 4 + (cc >> 2)), (it >> 1) & 1);   // this slab of h1 has landed
-          const uint32_t slab = sbase + kOffH1 + (uint32_t)hb * 65536u + (uint32_t)(cc >> 2) * 16384u + (uint32_t)r * 128u;
 #ifdef TDSSF_CH_NOE1   // (timing experiment: TMEM loads only)
           if (p.N < 0)
 #endif
 #pragma unroll
           for (int k = 0; k < 2; ++k) {
-            const uint32_t q = (uint32_t)(cc & 3) * 2u + k;
-            const uint32_t addr = slab + ((q ^ sw) << 4);
-            const uint4 h = ptx::lds128(addr);
-            ptx::sts128(addr, pack2(__uint_as_float(v[8 * k]), __uint_as_float(v[8 * k + 1])) & relu_mask2(h.x),
+            const int q = (cc & 3) * 2 + k;
+            const uint4 h = hq[q];
+            ptx::sts128(slab + (((uint32_t)q ^ sw) << 4), pack2(__uint_as_float(v[8 * k]), __uint_as_float(v[8 * k + 1])) & relu_mask2(h.x),
                         pack2(__uint_as_float(v[8 * k + 2]), __uint_as_float(v[8 * k + 3])) & relu_mask2(h.y),
                         pack2(__uint_as_float(v[8 * k + 4]), __uint_as_float(v[8 * k + 5])) & relu_mask2(h.z),
                         pack2(__uint_as_float(v[8 * k + 6]), __uint_as_float(v[8 * k + 7])) & relu_mask2(h.w));
@@ -270,9 +289,11 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
           }
         }
       }
+      if (warp == 0) CH_TRACE(1, it);
       // dx_pt
       wait_bar(bar(kAccxFull), it & 1);
       ptx::tc_fence_after();
+      if (warp == 0) CH_TRACE(2, it);
       uint32_t x0[16], x1[16];
       uint4* dst = reinterpret_cast<uint4*>(p.dx_pt + (row < p.N ? row : 0) * kCp);
       const bool store = p.dx_pt != nullptr && row < p.N;
@@ -298,16 +319,17 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
         (void)store; (void)dst;
 #endif
       }
+      if (warp == 0) CH_TRACE(3, it);
     }
   } else if (warp < 8) {
     // ------------------------------------------------ dh2 producers --------------------------------------------------
     const int i = threadIdx.x - 128;
     const uint32_t sw = (uint32_t)i & 7u;
-    const uint32_t w3 = sbase + kOffW3;
     const uint32_t slab = sbase + kOffDh2 + (uint32_t)i * 128u;
-    // The whole row is computed into registers BEFORE the wait for the slab (the previous tile's product and copy-out
-    // still read it), so that what sits between "slab free" and "slab full" is eight 16-byte stores.
-    ptx::u32x8 dn[2], hn[4];   // the next tile's dl row and h2 row, in flight while this tile is computed
+    // dl (fp32) -> bf16 -> the K = 16 A operand of dl @ W3 (one tcgen05.mma per tile, accumulator columns [320,384));
+    // then this warp is the epilogue of that product for its 32 rows: mask from h2, bf16, into the dh2 slab.  The next
+    // tile's dl / h2 rows are fetched while the product and the mask run.
+    ptx::u32x8 dn[2], hn[4];
     auto prefetch = [&](int it) {
       const int64_t row = tile_of(it) * 128 + i;
       const bool live = it < n_iters && row < p.N;
@@ -322,44 +344,40 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
         for (int e = 0; e < 8; ++e) { dn[0].v[e] = dn[1].v[e] = 0u; hn[0].v[e] = hn[1].v[e] = hn[2].v[e] = hn[3].v[e] = 0u; }
       }
     };
+    const uint32_t tl = tmem + (((uint32_t)(warp & 3) * 32u) << 16) + 320u;
+    const uint32_t dl_row = sbase + kOffDl + (uint32_t)(i >> 3) * 256u + (uint32_t)(i & 7) * 16u;
     prefetch(0);
-    wait_bar(bar(kWFull), 0);   // W3
     for (int it = 0; it < n_iters; ++it) {
-      float d[kC];
+      if (warp == 4) CH_TRACE(4, it);
+      // (the previous tile's product has completed: this warp waited for its accumulator, so the dl operand is free)
 #pragma unroll
-      for (int c = 0; c < kC; ++c) d[c] = __uint_as_float(dn[c >> 3].v[c & 7]);
+      for (int k = 0; k < 2; ++k)
+        ptx::sts128(dl_row + 128u * k, pack2(__uint_as_float(dn[k].v[0]), __uint_as_float(dn[k].v[1])),
+                    pack2(__uint_as_float(dn[k].v[2]), __uint_as_float(dn[k].v[3])), pack2(__uint_as_float(dn[k].v[4]), __uint_as_float(dn[k].v[5])),
+                    pack2(__uint_as_float(dn[k].v[6]), __uint_as_float(dn[k].v[7])));
+      ptx::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_local(bar(kDlFull));
+      __syncwarp();
+      uint32_t hm[32];   // the row's 64 ReLU masks (packed pairs); frees hn for the next tile's loads
+#pragma unroll
+      for (int k = 0; k < 32; ++k) hm[k] = relu_mask2(hn[k >> 3].v[k & 7]);
+      prefetch(it + 1);
+      wait_bar(bar(kAcc2Full), it & 1);
+      ptx::tc_fence_after();
+      if (warp == 4) CH_TRACE(5, it);
       uint32_t res[32];
 #pragma unroll
-      for (int k = 0; k < 32; ++k) res[k] = 0u;
-#pragma unroll 1
-      for (int qq = 0; qq < 4; ++qq) {   // sixteen output columns per pass (a real loop: the 64 W3 loads of a pass stay
-                                         // next to their use); the results shift through `res` so that every index is static
-        uint32_t fresh[8];
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[16];
+        ptx::tmem_ld16(tl + c * 16, v);
+        ptx::tmem_wait_ld();
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          float acc[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-#ifndef TDSSF_CH_NOPROD   // (timing experiment: no dl @ W3)
-          const uint32_t wq = w3 + (uint32_t)(qq * 16 + half * 8) * 4u;
-#pragma unroll
-          for (int c = 0; c < kC; ++c) {
-            const float4 wa = ptx::lds128_ro(wq + (uint32_t)(c * kN2) * 4u), wb = ptx::lds128_ro(wq + (uint32_t)(c * kN2 + 4) * 4u);
-            acc[0] = fmaf(d[c], wa.x, acc[0]); acc[1] = fmaf(d[c], wa.y, acc[1]); acc[2] = fmaf(d[c], wa.z, acc[2]); acc[3] = fmaf(d[c], wa.w, acc[3]);
-            acc[4] = fmaf(d[c], wb.x, acc[4]); acc[5] = fmaf(d[c], wb.y, acc[5]); acc[6] = fmaf(d[c], wb.z, acc[6]); acc[7] = fmaf(d[c], wb.w, acc[7]);
-          }
-#endif
-#pragma unroll
-          for (int k = 0; k < 4; ++k) fresh[4 * half + k] = pack2(acc[2 * k], acc[2 * k + 1]) & relu_mask2(hn[0].v[4 * half + k]);
-        }
-#pragma unroll
-        for (int k = 0; k < 24; ++k) res[k] = res[k + 8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) res[24 + k] = fresh[k];
-        hn[0] = hn[1]; hn[1] = hn[2]; hn[2] = hn[3];
+        for (int k = 0; k < 8; ++k) res[8 * c + k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1])) & hm[8 * c + k];
       }
-      prefetch(it + 1);
+      ptx::tc_fence_before();
       if (it >= 1) wait_bar(bar(kDh2Free), (it - 1) & 1);
+      if (warp == 4) CH_TRACE(6, it);
 #pragma unroll
       for (int q = 0; q < 8; ++q)
         ptx::sts128(slab + (((uint32_t)q ^ sw) << 4), res[4 * q], res[4 * q + 1], res[4 * q + 2], res[4 * q + 3]);
@@ -367,27 +385,42 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Full));
       __syncwarp();
+      if (warp == 4) CH_TRACE(7, it);
     }
   } else if (warp == 8) {
     // ------------------------------------------------ MMA issue ------------------------------------------------------
     if (lane == 0) {
-      constexpr uint32_t kI1 = ptx::idesc_bf16(128, kN1), kIx = ptx::idesc_bf16(128, kCp);
+      constexpr uint32_t kI1 = ptx::idesc_bf16(128, kN1), kIx = ptx::idesc_bf16(128, kCp), kI2 = ptx::idesc_bf16(128, kN2);
+      // dl @ W3 of tile `it`: one K = 16 instruction on the no-swizzle operands, accumulator columns [320,384)
+      auto issue_l2 = [&](int it) {
+        wait_bar(bar(kDlFull), it & 1);
+        ptx::tc_fence_after();
+        ptx::umma_ss_1cta(tmem + 320, ptx::smem_desc_nosw(sbase + kOffDl, 128, 256), ptx::smem_desc_nosw(sbase + kOffW3, 128, 256), kI2, 0);
+        ptx::umma_commit_1cta(bar(kAcc2Full));
+      };
       wait_bar(bar(kWFull), 0);
+      if (n_iters > 0) issue_l2(0);
       for (int it = 0; it < n_iters; ++it) {
         const int hb = it & 1;
         wait_bar(bar(kDh2Full), it & 1);
+        // the next tile's dl @ W3 first: its operand arrives right after this tile's dh2 slab, and its accumulator was read
+        // before that slab was announced - the producers' masks then overlap the wait for the previous tile's epilogue
+        if (it + 1 < n_iters) issue_l2(it + 1);
         if (it >= 1) wait_bar(bar(kAcc1Free), (it - 1) & 1);
         ptx::tc_fence_after();
+        CH_TRACE(8, it);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
           ptx::umma_ss_1cta(tmem, ptx::smem_desc_sw128(sbase + kOffDh2 + kk * 32), ptx::smem_desc_sw128(sbase + kOffW2t + kk * 32), kI1, kk != 0);
         ptx::umma_commit_1cta(bar(kAcc1Full));
         ptx::umma_commit_1cta(bar(kDh2Free));
+        CH_TRACE(9, it);
         if (it >= 1) wait_bar(bar(kAccxFree), (it - 1) & 1);
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
           wait_bar(bar(kDh1Full + s), it & 1);
           ptx::tc_fence_after();
+          if (s == 0) CH_TRACE(10, it);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
             ptx::umma_ss_1cta(tmem + 256, ptx::smem_desc_sw128(sbase + kOffH1 + hb * 65536 + s * 16384 + kk * 32),
@@ -395,6 +428,7 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
           ptx::umma_commit_1cta(bar(kH1Free + hb * 4 + s));
         }
         ptx::umma_commit_1cta(bar(kAccxFull));
+        CH_TRACE(11, it);
       }
     }
     __syncwarp();
@@ -406,6 +440,7 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
           if (it >= 2) wait_bar(bar(kH1Free + hb * 4 + s), ((it >> 1) - 1) & 1);
+          if (s == 0) CH_TRACE(16, it);
           ptx::mbar_expect_tx(bar(kH1Full + hb * 4 + s), 16384);
           ptx::tma_load_2d(sbase + kOffH1 + hb * 65536 + s * 16384, &tm_h1, 64 * s, (int)(tile_of(it) * 128), bar(kH1Full + hb * 4 + s));
         }
@@ -423,24 +458,36 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
 #ifdef TDSSF_CH_NODRAIN   // (timing experiment: helpers only run the barrier protocol)
       if (p.N >= 0) return;
 #endif
-#pragma unroll 4
-      for (int r = r_lo + rg; r < r_hi; r += 4) {
-        const uint4 v = ptx::lds128(slab + (uint32_t)r * 128u + ((((uint32_t)q) ^ ((uint32_t)r & 7u)) << 4));
-        acc[0] += bf_lo(v.x); acc[1] += bf_hi(v.x); acc[2] += bf_lo(v.y); acc[3] += bf_hi(v.y);
-        acc[4] += bf_lo(v.z); acc[5] += bf_hi(v.z); acc[6] += bf_lo(v.w); acc[7] += bf_hi(v.w);
-        if (row0 + r < p.N) *reinterpret_cast<uint4*>(out + (row0 + r) * ld + col0 + q * 8) = v;
+      for (int r4 = r_lo + rg; r4 < r_hi; r4 += 16) {   // four loads in flight, then their sums and stores
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int r = r4 + 4 * u;
+          v[u] = ptx::lds128(slab + (uint32_t)r * 128u + ((((uint32_t)q) ^ ((uint32_t)r & 7u)) << 4));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int r = r4 + 4 * u;
+          acc[0] += bf_lo(v[u].x); acc[1] += bf_hi(v[u].x); acc[2] += bf_lo(v[u].y); acc[3] += bf_hi(v[u].y);
+          acc[4] += bf_lo(v[u].z); acc[5] += bf_hi(v[u].z); acc[6] += bf_lo(v[u].w); acc[7] += bf_hi(v[u].w);
+          if (row0 + r < p.N) *reinterpret_cast<uint4*>(out + (row0 + r) * ld + col0 + q * 8) = v[u];
+        }
       }
     };
     for (int it = 0; it < n_iters; ++it) {
       const int hb = it & 1;
       const int64_t row0 = tile_of(it) * 128;
       wait_bar(bar(kDh2Full), it & 1);
+      if (h == 0) CH_TRACE(12, it);
       drain(sbase + kOffDh2, p.dh2_out, kN2, 0, row0, 32 * h, 32 * h + 32, s2);
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_local(bar(kDh2Free));
       __syncwarp();
+      if (h == 0) CH_TRACE(13, it);
       wait_bar(bar(kDh1Full + h), it & 1);
+      if (h == 0) CH_TRACE(14, it);
       drain(sbase + kOffH1 + hb * 65536 + h * 16384, p.dh1_out, kN1, h * 64, row0, 0, 128, s1);
+      if (h == 0) CH_TRACE(15, it);
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_local(bar(kH1Free + hb * 4 + h));
       __syncwarp();
@@ -452,12 +499,20 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
       s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], 8);
       s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], 16);
     }
-    if (rg == 0 && n_iters > 0) {
+    // per-CTA partial sums (no atomics: 148 CTAs finishing together would serialise on 320 addresses); db2 of the four
+    // copy-out warps goes through shared memory (the dl operand buffer is idle by now)
+    float* s_db2 = reinterpret_cast<float*>(smem + kOffDl);
+    float* bp = p.bias_partial + (size_t)blockIdx.x * 320;
+    if (rg == 0) {
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        atomicAdd(p.db1 + h * 64 + q * 8 + e, s1[e]);
-        atomicAdd(p.db2 + q * 8 + e, s2[e]);
+        bp[h * 64 + q * 8 + e] = s1[e];
+        s_db2[h * 64 + q * 8 + e] = s2[e];
       }
+    }
+    ptx::named_bar_sync(1, 128);
+    if (h == 0) {
+      for (int c = lane; c < 64; c += 32) bp[256 + c] = (s_db2[c] + s_db2[64 + c]) + (s_db2[128 + c] + s_db2[192 + c]);
     }
   }
 
@@ -637,8 +692,26 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tm_dh1, const __grid_constant__
 // One thread per output element, partials added in CTA order (deterministic).
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const float* __restrict__ partials, int n_a, int n_cta, float* __restrict__ dW1, float* __restrict__ dW2,
-                    const float* __restrict__ partials3, int n3, float* __restrict__ dW3, float* __restrict__ db3) {
+                    const float* __restrict__ partials3, int n3, float* __restrict__ dW3, float* __restrict__ db3,
+                    const float* __restrict__ bias_partials, int n_chain, float* __restrict__ db1, float* __restrict__ db2) {
   constexpr int kMainBlocks = (kN1 * kK1 + kN1 * kN2 + 255) / 256;
+  constexpr int kW3Blocks = (kW3Out + 31) / 32;
+  if ((int)blockIdx.x >= kMainBlocks + kW3Blocks) {
+    // db1 / db2: 32 outputs per block from the chain kernel's per-CTA column sums, same scheme as dW3 below
+    __shared__ float s[8][32];
+    const int o = ((int)blockIdx.x - kMainBlocks - kW3Blocks) * 32 + (threadIdx.x & 31), k = threadIdx.x >> 5;
+    float v = 0.f;
+    for (int b = k; b < n_chain; b += 8) v += bias_partials[(size_t)b * 320 + o];
+    s[k][threadIdx.x & 31] = v;
+    __syncthreads();
+    if (k == 0) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += s[j][threadIdx.x];
+      if (o < 256) db1[o] += t; else db2[o - 256] += t;
+    }
+    return;
+  }
   if ((int)blockIdx.x >= kMainBlocks) {
     // dW3 / db3: 32 outputs per block, eight threads per output walk the dw3_db3_kernel partials, then a shared-memory sum
     __shared__ float s[8][32];
@@ -717,6 +790,7 @@ struct Work {
   uint8_t* chain_w;
   float* partials;
   float* partials3;
+  float* bias_partials;
 };
 static size_t al(size_t b) { return (b + 255) & ~(size_t)255; }
 static size_t carve(int64_t N, int n_cta, char* base, Work* w) {
@@ -728,7 +802,8 @@ static size_t carve(int64_t N, int n_cta, char* base, Work* w) {
   uint8_t* cw = (uint8_t*)take(kChainWeightBytes);
   float* partials = (float*)take((size_t)n_cta * wg::kPartialFloats * 4);
   float* partials3 = (float*)take((size_t)kMaxW3Blocks * kW3Out * 4);
-  if (w) *w = Work{X, dh2, dh1, cw, partials, partials3};
+  float* bias_partials = (float*)take((size_t)1024 * 320 * 4);
+  if (w) *w = Work{X, dh2, dh1, cw, partials, partials3, bias_partials};
   return off;
 }
 // the weight-gradient grid: one CTA per SM, at most one per stage of 64 points and at least one of each flavour
@@ -791,17 +866,45 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     return TDSSF_ECUDA;
   }
 
-  // 1. data-gradient chain (writes dh2, dh1, dx_pt; accumulates db2, db1)
+  // 1. data-gradient chain (writes dh2, dh1, dx_pt and per-CTA bias sums)
+  int n_chain = 0;
   {
     static bool done[kMaxDevices] = {};
     if (int rc = set_smem(chain::dgrad_chain_kernel, chain::kSmemBytes + 1024, done)) return rc;
     chain::Params p = {};
     p.dl = dlogits; p.h2 = reinterpret_cast<const uint16_t*>(h2_bf16); p.weights = w.chain_w;
-    p.dh2_out = w.dh2; p.dh1_out = w.dh1; p.dx_pt = dx_pt; p.db1 = g_host->db1; p.db2 = g_host->db2;
+    p.dh2_out = w.dh2; p.dh1_out = w.dh1; p.dx_pt = dx_pt; p.bias_partial = w.bias_partials;
     p.N = N; p.n_tiles = (int)ceil_div(N, 128);
     const int grid = std::min(num_sms(), p.n_tiles);
+    n_chain = grid;
+#ifdef TDSSF_CH_TRACE
+    static long long* trace = nullptr;
+    if (!trace) { cudaMalloc(&trace, 17 * 16 * 8); }
+    cudaMemsetAsync(trace, 0, 17 * 16 * 8, s);
+    p.trace = trace;
+#endif
     chain::dgrad_chain_kernel<<<grid, chain::kThreads, chain::kSmemBytes + 1024, s>>>(tm_h1_128, p);
     TDSSF_LAUNCH_CHECK();
+#ifdef TDSSF_CH_TRACE
+    {
+      static int calls = 0;
+      if (++calls == 6) {
+        long long h[17 * 16];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(h, trace, sizeof(h), cudaMemcpyDeviceToHost);
+        const char* names[17] = {"epi acc1 full", "epi E1 done", "epi accx full", "epi Ex done", "prod start", "prod computed", "prod slab free",
+                                 "prod arrived", "mma dh2+acc1free", "mma L1 issued", "mma dh1 slab0", "mma Lx issued", "help dh2 full",
+                                 "help dh2 drained", "help dh1 slab0", "help dh1 drained", "tma issue"};
+        long long t0 = h[4 * 16];
+        fprintf(stderr, "[chain trace] CTA 0, cycles since the producer's first start; tiles 0..7\n");
+        for (int e = 0; e < 17; ++e) {
+          fprintf(stderr, "  %-18s", names[e]);
+          for (int it = 0; it < 8; ++it) fprintf(stderr, " %8lld", h[e * 16 + it] ? h[e * 16 + it] - t0 : -1);
+          fprintf(stderr, "\n");
+        }
+      }
+    }
+#endif
   }
   // 2. dW3, db3 on the CUDA cores
   const int n3 = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(num_sms() * 2, kMaxW3Blocks), ceil_div(N, 256)));
@@ -816,8 +919,9 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     p.n_a = std::max(1, std::min(n_cta - 1, (n_cta * 2 + 2) / 5));   // bytes per stage 8 : 12 slabs -> CTAs 2 : 3
     wg::wgrad_kernel<<<n_cta, wg::kThreads, wg::kSmemBytes + 1024, s>>>(tm_dh1, tm_x, tm_h1, tm_dh2, p);
     TDSSF_LAUNCH_CHECK();
-    wg::wgrad_reduce_kernel<<<(kN1 * kK1 + kN1 * kN2 + 255) / 256 + (kW3Out + 31) / 32, 256, 0, s>>>(
-        w.partials, p.n_a, n_cta, g_host->dW1, g_host->dW2, w.partials3, n3, g_host->dW3, g_host->db3);
+    wg::wgrad_reduce_kernel<<<(kN1 * kK1 + kN1 * kN2 + 255) / 256 + (kW3Out + 31) / 32 + 10, 256, 0, s>>>(
+        w.partials, p.n_a, n_cta, g_host->dW1, g_host->dW2, w.partials3, n3, g_host->dW3, g_host->db3, w.bias_partials, n_chain,
+        g_host->db1, g_host->db2);
     TDSSF_LAUNCH_CHECK();
   }
   return TDSSF_OK;

@@ -184,6 +184,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128_ex(uint32_t smem_addr, uint3
   d |= (uint64_t)2 << 61;   // SWIZZLE_128B
   return d;
 }
+// K-major operand without swizzle ("interleaved" canonical layout, cute/atom/mma_traits_sm100.hpp: ((8,m),(T,2)):((1T,SBO),(1,LBO))):
+// 8 x 16-byte core matrices (row r of a core at +16 r); the second 8 K elements of a K = 16 step `lbo` bytes further,
+// the next 8 rows `sbo` bytes further
+__device__ __forceinline__ uint64_t smem_desc_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;   // descriptor version (sm_100); layout type 0 = no swizzle
+  return d;
+}
 // instruction descriptor bits for MN-major operands (cute/arch/mma_sm100_desc.hpp: a_major bit 15, b_major bit 16)
 constexpr uint32_t kIdescAMajorMN = 1u << 15, kIdescBMajorMN = 1u << 16;
 
