@@ -15,6 +15,9 @@
 // Everything is HBM-bound integer / fp32 work; there is no tensor-core stage.
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
+#include <string.h>
+
 #include "common.cuh"
 
 namespace tdssf {
@@ -46,6 +49,7 @@ struct CelsWs {
   uint32_t* vals[2];    // [16*N]
   uint32_t* hist;       // [16][kBins][sort_tiles]
   int* tile_fg;         // [16][sort_tiles]
+  int stride;           // distance between the per-class segments of keys / vals: n_valid (exact mode) or n_rows (device-count mode)
 };
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -275,7 +279,7 @@ lovasz_select_kernel(CelsWs ws, int tiles) {
     if ((sel >> c) & 1u) {
       int before = ws.sel_tile[c * tiles + blockIdx.x];
       for (int ww = 0; ww < w; ++ww) before += s_wc[ww][c];
-      const int64_t pos = (int64_t)c * N + before + rank[c];
+      const int64_t pos = (int64_t)c * ws.stride + before + rank[c];
       ws.keys[0][pos] = key[c];
       ws.vals[0][pos] = (uint32_t)i;
     }
@@ -611,85 +615,236 @@ extern "C" size_t tdssf_cels_workspace_bytes(int64_t n_rows) {
   return tdssf::carve(nullptr, nullptr, std::max<int64_t>(n_rows, 1));
 }
 
+namespace tdssf {
+
+struct CelsArgs {
+  const float* logits; const int64_t* labels; const uint8_t* mask; int64_t n_rows; const float* class_w; float lambda; int ignore;
+  float* out_scalars; int64_t* preds; int64_t* gt; float* dlogits; void* workspace;
+  bool operator==(const CelsArgs& o) const { return memcmp(this, &o, sizeof(CelsArgs)) == 0; }
+};
+
+// stage 1: valid-row flags per tile and their exclusive scan; *ws.n_valid = number of rows that survive mask & label != ignore
+static int cels_stage_count(const CelsArgs& a, const CelsWs& ws, cudaStream_t s) {
+  // n_valid, class_count, fg_keymax, seg_count and acc are carved next to each other: one memset
+  TDSSF_CUDA(cudaMemsetAsync(ws.n_valid, 0, (size_t)(reinterpret_cast<char*>(ws.acc + 18) - reinterpret_cast<char*>(ws.n_valid)), s));
+  if (a.n_rows > 0) {
+    const unsigned row_tiles = (unsigned)ceil_div(a.n_rows, kRowTile);
+    cels_count_kernel<<<row_tiles, kRowTile, 0, s>>>(a.labels, a.mask, a.n_rows, a.ignore, ws.tile_count);
+    TDSSF_LAUNCH_CHECK();
+    scan_ints_kernel<<<1, 256, 0, s>>>(ws.tile_count, ws.tile_offset, row_tiles, ws.n_valid);
+    TDSSF_LAUNCH_CHECK();
+  }
+  return TDSSF_OK;
+}
+
+// stage 2: everything after the count.  `bound` = number of compact rows the grids and the segment stride are sized for:
+// the exact n_valid when the host has read it (tdssf_cels_fwd_bwd), or n_rows when it has not (device-count mode: every
+// kernel takes its real bounds from the counts in the workspace, the surplus CTAs return at once) - the same results.
+static int cels_stage_main(const CelsArgs& a, CelsWs ws, int64_t bound, cudaStream_t s) {
+  if (a.dlogits && a.n_rows) TDSSF_CUDA(cudaMemsetAsync(a.dlogits, 0, (size_t)a.n_rows * kC * sizeof(float), s));
+  if (bound > 0) {
+    const int N = (int)bound;
+    ws.stride = N;
+    const unsigned row_tiles = (unsigned)ceil_div(a.n_rows, kRowTile);
+    cels_compact_kernel<<<row_tiles, kRowTile, 0, s>>>(a.logits, a.labels, a.mask, a.n_rows, a.ignore, a.class_w, ws, a.preds, a.gt);
+    TDSSF_LAUNCH_CHECK();
+    // TDSSF_CELS_SELECT=all (tests): every key of a present class is sorted, as the reference does
+    const char* sel_mode = getenv("TDSSF_CELS_SELECT");
+    if (sel_mode && sel_mode[0] == 'a') TDSSF_CUDA(cudaMemsetAsync(ws.fg_keymax, 0xff, kC * sizeof(uint32_t), s));
+    const int sel_tiles = (int)ceil_div(N, kRowTile);
+    lovasz_select_kernel<false><<<sel_tiles, kRowTile, 0, s>>>(ws, sel_tiles);
+    TDSSF_LAUNCH_CHECK();
+    lovasz_segscan_kernel<<<kC, 256, 0, s>>>(ws, sel_tiles);
+    TDSSF_LAUNCH_CHECK();
+    lovasz_select_kernel<true><<<sel_tiles, kRowTile, 0, s>>>(ws, sel_tiles);
+    TDSSF_LAUNCH_CHECK();
+    const int tiles = (int)ceil_div(N, kSortTile);   // upper bound: the kernels read the selected count per class
+    const dim3 sgrid((unsigned)tiles, kC);
+    int cur = 0;
+    // beyond kFusedScanTiles the per-CTA prefix reads would grow quadratically (TDSSF_CELS_SCAN=separate: tests)
+    const char* scan_mode = getenv("TDSSF_CELS_SCAN");
+    const bool fused_scan = tiles <= kFusedScanTiles && !(scan_mode && scan_mode[0] == 's');
+    for (int pass = 0; pass < kPasses; ++pass) {
+      const int shift = pass * kRadixBits;
+      sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, ws.seg_count, shift, tiles, ws.class_count, ws.hist, fused_scan);
+      TDSSF_LAUNCH_CHECK();
+      if (!fused_scan) {
+        sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count, ws.seg_count);
+        TDSSF_LAUNCH_CHECK();
+      }
+      sort_scatter_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1],
+                                                         N, ws.seg_count, shift, tiles, ws.class_count, ws.hist, fused_scan);
+      TDSSF_LAUNCH_CHECK();
+      cur ^= 1;
+    }
+    TDSSF_CUDA(cudaMemsetAsync(ws.dprob, 0, (size_t)N * kC * sizeof(float), s));
+    lovasz_fgcount_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.vals[cur], ws.ylab, N, ws.seg_count, tiles, ws.class_count, ws.tile_fg);
+    TDSSF_LAUNCH_CHECK();
+    lovasz_tilescan_kernel<<<kC, 256, 0, s>>>(ws.tile_fg, tiles, ws.class_count);
+    TDSSF_LAUNCH_CHECK();
+    lovasz_grad_dot_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.ylab, N, ws.seg_count, tiles, ws.class_count,
+                                                          ws.tile_fg, ws.dprob, ws.acc);
+    TDSSF_LAUNCH_CHECK();
+    if (a.dlogits) {
+      cels_backward_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, s>>>(ws, a.class_w, 1.f, a.lambda, nullptr, a.dlogits);
+      TDSSF_LAUNCH_CHECK();
+    }
+  }
+  cels_finalize_kernel<<<1, 1, 0, s>>>(ws, a.lambda, a.out_scalars);
+  TDSSF_LAUNCH_CHECK();
+  return TDSSF_OK;
+}
+
+static int cels_check(const CelsArgs& a, size_t workspace_bytes, const char* who) {
+  TDSSF_REQUIRE(a.n_rows >= 0 && a.n_rows < (int64_t)1 << 27, "%s: n_rows=%lld out of range", who, (long long)a.n_rows);
+  TDSSF_REQUIRE(a.out_scalars && a.class_w && a.workspace, "%s: NULL pointer", who);
+  TDSSF_REQUIRE(workspace_bytes >= tdssf_cels_workspace_bytes(a.n_rows), "%s: workspace too small", who);
+  if (a.n_rows > 0) {
+    TDSSF_REQUIRE(a.logits && a.labels && a.preds && a.gt, "%s: NULL input/output", who);
+    TDSSF_REQUIRE(((uintptr_t)a.logits & 15) == 0 && (!a.dlogits || ((uintptr_t)a.dlogits & 15) == 0), "%s: logits/dlogits must be 16-byte aligned", who);
+  }
+  return TDSSF_OK;
+}
+
+// ---- device-count mode as a CUDA graph --------------------------------------------------------------------------
+// The launch sequence of stage 2 depends only on the argument values (pointers, n_rows), not on the data: when a call
+// repeats the arguments of an earlier one (a training loop: the caching allocator hands out the same blocks every
+// step, or alternates between a few) the sequence is captured once into a graph and replayed - one launch instead of
+// about twenty-five.
+struct CelsGraph { CelsArgs key; int device; cudaGraphExec_t exec; unsigned long long used; };
+constexpr int kGraphSlots = 8;
+static CelsGraph g_graphs[kGraphSlots];
+static CelsArgs g_seen[kGraphSlots];   // argument sets of recent plain calls (a loop whose buffers alternate between two or
+static int g_seen_dev[kGraphSlots];    // three allocator blocks repeats with that period, not every call)
+static int g_seen_next = 0;
+static unsigned long long g_tick = 0;
+static long long g_stats[3] = {0, 0, 0};   // replays, captures, plain launch sequences
+static std::mutex g_graph_mu;
+
+static int cels_stage_main_graphed(const CelsArgs& a, const CelsWs& ws, cudaStream_t s) {
+  const char* env = getenv("TDSSF_CELS_GRAPH");
+  if (env && env[0] == '0') return cels_stage_main(a, ws, a.n_rows, s);
+  std::lock_guard<std::mutex> lock(g_graph_mu);
+  const int dev = current_device();
+  ++g_tick;
+  for (auto& g : g_graphs)
+    if (g.exec && g.device == dev && g.key == a) {
+      g.used = g_tick;
+      ++g_stats[0];
+      TDSSF_CUDA(cudaGraphLaunch(g.exec, s));
+      return TDSSF_OK;
+    }
+  bool repeat = false;
+  for (int i = 0; i < kGraphSlots; ++i) repeat |= g_seen_dev[i] == dev + 1 && g_seen[i] == a;
+  if (!repeat) {
+    g_seen[g_seen_next] = a;
+    g_seen_dev[g_seen_next] = dev + 1;
+    g_seen_next = (g_seen_next + 1) % kGraphSlots;
+  }
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  // (a caller whose buffers never settle would pay a capture per call: stop capturing when replays do not follow)
+  const bool thrash = g_stats[1] >= 8 && g_stats[0] < 4 * g_stats[1];
+  if (!repeat || thrash || (s != nullptr && (cudaStreamIsCapturing(s, &st) != cudaSuccess || st != cudaStreamCaptureStatusNone))) {
+    ++g_stats[2];
+    return cels_stage_main(a, ws, a.n_rows, s);
+  }   // first sighting (or the caller is capturing itself): plain launches
+  // captured on a private stream (the caller's may be the legacy default stream, which cannot be captured); the graph
+  // itself is launched into the caller's stream
+  static cudaStream_t cap[kMaxDevices] = {};
+  if (!cap[dev] && cudaStreamCreateWithFlags(&cap[dev], cudaStreamNonBlocking) != cudaSuccess) {
+    cap[dev] = nullptr;
+    cudaGetLastError();
+    return cels_stage_main(a, ws, a.n_rows, s);
+  }
+  CelsGraph* slot = &g_graphs[0];
+  for (auto& g : g_graphs)
+    if (!g.exec) { slot = &g; break; } else if (g.used < slot->used) slot = &g;
+  if (slot->exec) { cudaGraphExecDestroy(slot->exec); slot->exec = nullptr; }
+  cudaGraph_t graph = nullptr;
+  if (cudaStreamBeginCapture(cap[dev], cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    return cels_stage_main(a, ws, a.n_rows, s);
+  }
+  const int rc = cels_stage_main(a, ws, a.n_rows, cap[dev]);
+  const cudaError_t e = cudaStreamEndCapture(cap[dev], &graph);
+  if (rc != TDSSF_OK || e != cudaSuccess || !graph) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    return rc != TDSSF_OK ? rc : cels_stage_main(a, ws, a.n_rows, s);
+  }
+  cudaGraphExec_t exec = nullptr;
+  const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ei != cudaSuccess || !exec) {
+    cudaGetLastError();
+    return cels_stage_main(a, ws, a.n_rows, s);
+  }
+  *slot = CelsGraph{a, dev, exec, g_tick};
+  ++g_stats[1];
+  TDSSF_CUDA(cudaGraphLaunch(exec, s));
+  return TDSSF_OK;
+}
+
+}  // namespace tdssf
+
 extern "C" int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, const uint8_t* mask,
                                   int64_t n_rows, const float* class_w, float lambda_lovasz, int ignore_index,
                                   float* out_scalars, int64_t* n_valid_host, int64_t* preds, int64_t* gt,
                                   float* dlogits, void* workspace, size_t workspace_bytes, void* stream) {
   using namespace tdssf;
-  TDSSF_REQUIRE(n_rows >= 0 && n_rows < (int64_t)1 << 27, "tdssf_cels_fwd_bwd: n_rows=%lld out of range", (long long)n_rows);
-  TDSSF_REQUIRE(out_scalars && n_valid_host && class_w && workspace, "tdssf_cels_fwd_bwd: NULL pointer");
-  TDSSF_REQUIRE(workspace_bytes >= tdssf_cels_workspace_bytes(n_rows), "tdssf_cels_fwd_bwd: workspace too small");
+  TDSSF_REQUIRE(n_valid_host, "tdssf_cels_fwd_bwd: NULL n_valid_host");
+  const CelsArgs a = {logits, labels, mask, n_rows, class_w, lambda_lovasz, ignore_index, out_scalars, preds, gt, dlogits, workspace};
+  if (int rc = cels_check(a, workspace_bytes, "tdssf_cels_fwd_bwd")) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   CelsWs ws;
   char* base = reinterpret_cast<char*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   carve(&ws, base, std::max<int64_t>(n_rows, 1));
-  // n_valid, class_count, fg_keymax, seg_count and acc are carved next to each other: one memset
-  TDSSF_CUDA(cudaMemsetAsync(ws.n_valid, 0, (size_t)(reinterpret_cast<char*>(ws.acc + 18) - reinterpret_cast<char*>(ws.n_valid)), s));
-  if (dlogits && n_rows) TDSSF_CUDA(cudaMemsetAsync(dlogits, 0, (size_t)n_rows * kC * sizeof(float), s));
+  if (int rc = cels_stage_count(a, ws, s)) return rc;
+  int n_valid = 0;
   *n_valid_host = 0;
   if (n_rows > 0) {
-    TDSSF_REQUIRE(logits && labels && preds && gt, "tdssf_cels_fwd_bwd: NULL input/output");
-    TDSSF_REQUIRE(((uintptr_t)logits & 15) == 0 && (!dlogits || ((uintptr_t)dlogits & 15) == 0),
-                  "tdssf_cels_fwd_bwd: logits/dlogits must be 16-byte aligned");
-    const unsigned row_tiles = (unsigned)ceil_div(n_rows, kRowTile);
-    cels_count_kernel<<<row_tiles, kRowTile, 0, s>>>(labels, mask, n_rows, ignore_index, ws.tile_count);
-    TDSSF_LAUNCH_CHECK();
-    scan_ints_kernel<<<1, 256, 0, s>>>(ws.tile_count, ws.tile_offset, row_tiles, ws.n_valid);
-    TDSSF_LAUNCH_CHECK();
-    int n_valid = 0;
     TDSSF_CUDA(cudaMemcpyAsync(&n_valid, ws.n_valid, sizeof(int), cudaMemcpyDeviceToHost, s));
     TDSSF_CUDA(cudaStreamSynchronize(s));  // the reference's boolean indexing synchronises here as well
     *n_valid_host = n_valid;
-    if (n_valid > 0) {
-      const int N = n_valid;
-      cels_compact_kernel<<<row_tiles, kRowTile, 0, s>>>(logits, labels, mask, n_rows, ignore_index, class_w, ws, preds, gt);
-      TDSSF_LAUNCH_CHECK();
-      // TDSSF_CELS_SELECT=all (tests): every key of a present class is sorted, as the reference does
-      const char* sel_mode = getenv("TDSSF_CELS_SELECT");
-      if (sel_mode && sel_mode[0] == 'a') TDSSF_CUDA(cudaMemsetAsync(ws.fg_keymax, 0xff, kC * sizeof(uint32_t), s));
-      const int sel_tiles = (int)ceil_div(N, kRowTile);
-      lovasz_select_kernel<false><<<sel_tiles, kRowTile, 0, s>>>(ws, sel_tiles);
-      TDSSF_LAUNCH_CHECK();
-      lovasz_segscan_kernel<<<kC, 256, 0, s>>>(ws, sel_tiles);
-      TDSSF_LAUNCH_CHECK();
-      lovasz_select_kernel<true><<<sel_tiles, kRowTile, 0, s>>>(ws, sel_tiles);
-      TDSSF_LAUNCH_CHECK();
-      const int tiles = (int)ceil_div(N, kSortTile);   // upper bound: the kernels read the selected count per class
-      const dim3 sgrid((unsigned)tiles, kC);
-      int cur = 0;
-      // beyond kFusedScanTiles the per-CTA prefix reads would grow quadratically (TDSSF_CELS_SCAN=separate: tests)
-      const char* scan_mode = getenv("TDSSF_CELS_SCAN");
-      const bool fused_scan = tiles <= kFusedScanTiles && !(scan_mode && scan_mode[0] == 's');
-      for (int pass = 0; pass < kPasses; ++pass) {
-        const int shift = pass * kRadixBits;
-        sort_hist_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], N, ws.seg_count, shift, tiles, ws.class_count, ws.hist, fused_scan);
-        TDSSF_LAUNCH_CHECK();
-        if (!fused_scan) {
-          sort_scan_kernel<<<kC, 256, 0, s>>>(ws.hist, tiles, ws.class_count, ws.seg_count);
-          TDSSF_LAUNCH_CHECK();
-        }
-        sort_scatter_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1],
-                                                           N, ws.seg_count, shift, tiles, ws.class_count, ws.hist, fused_scan);
-        TDSSF_LAUNCH_CHECK();
-        cur ^= 1;
-      }
-      TDSSF_CUDA(cudaMemsetAsync(ws.dprob, 0, (size_t)N * kC * sizeof(float), s));
-      lovasz_fgcount_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.vals[cur], ws.ylab, N, ws.seg_count, tiles, ws.class_count, ws.tile_fg);
-      TDSSF_LAUNCH_CHECK();
-      lovasz_tilescan_kernel<<<kC, 256, 0, s>>>(ws.tile_fg, tiles, ws.class_count);
-      TDSSF_LAUNCH_CHECK();
-      lovasz_grad_dot_kernel<<<sgrid, kSortThreads, 0, s>>>(ws.keys[cur], ws.vals[cur], ws.ylab, N, ws.seg_count, tiles, ws.class_count,
-                                                            ws.tile_fg, ws.dprob, ws.acc);
-      TDSSF_LAUNCH_CHECK();
-      if (dlogits) {
-        cels_backward_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, s>>>(ws, class_w, 1.f, lambda_lovasz, nullptr, dlogits);
-        TDSSF_LAUNCH_CHECK();
-      }
-    }
   }
-  cels_finalize_kernel<<<1, 1, 0, s>>>(ws, lambda_lovasz, out_scalars);
-  TDSSF_LAUNCH_CHECK();
+  return cels_stage_main(a, ws, n_valid, s);
+}
+
+extern "C" void tdssf_cels_graph_stats(int64_t* replays, int64_t* captures, int64_t* plain) {
+  std::lock_guard<std::mutex> lock(tdssf::g_graph_mu);
+  if (replays) *replays = tdssf::g_stats[0];
+  if (captures) *captures = tdssf::g_stats[1];
+  if (plain) *plain = tdssf::g_stats[2];
+}
+
+extern "C" int tdssf_cels_count(const int64_t* labels, const uint8_t* mask, int64_t n_rows, int ignore_index, int32_t* n_valid_dev,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace tdssf;
+  TDSSF_REQUIRE(n_rows >= 0 && n_rows < (int64_t)1 << 27, "tdssf_cels_count: n_rows=%lld out of range", (long long)n_rows);
+  TDSSF_REQUIRE(workspace && n_valid_dev && (labels || n_rows == 0), "tdssf_cels_count: NULL pointer");
+  TDSSF_REQUIRE(workspace_bytes >= tdssf_cels_workspace_bytes(n_rows), "tdssf_cels_count: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  CelsWs ws;
+  char* base = reinterpret_cast<char*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  carve(&ws, base, std::max<int64_t>(n_rows, 1));
+  CelsArgs a = {};
+  a.labels = labels; a.mask = mask; a.n_rows = n_rows; a.ignore = ignore_index;
+  if (int rc = cels_stage_count(a, ws, s)) return rc;
+  TDSSF_CUDA(cudaMemcpyAsync(n_valid_dev, ws.n_valid, sizeof(int), cudaMemcpyDeviceToDevice, s));
   return TDSSF_OK;
+}
+
+extern "C" int tdssf_cels_fwd_bwd_counted(const float* logits, const int64_t* labels, const uint8_t* mask,
+                                          int64_t n_rows, const float* class_w, float lambda_lovasz, int ignore_index,
+                                          float* out_scalars, int64_t* preds, int64_t* gt,
+                                          float* dlogits, void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace tdssf;
+  const CelsArgs a = {logits, labels, mask, n_rows, class_w, lambda_lovasz, ignore_index, out_scalars, preds, gt, dlogits, workspace};
+  if (int rc = cels_check(a, workspace_bytes, "tdssf_cels_fwd_bwd_counted")) return rc;
+  CelsWs ws;
+  char* base = reinterpret_cast<char*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  carve(&ws, base, std::max<int64_t>(n_rows, 1));
+  return cels_stage_main_graphed(a, ws, (cudaStream_t)stream);
 }
 
 extern "C" int tdssf_cels_backward(const void* workspace, size_t workspace_bytes, int64_t n_rows, int64_t n_valid,

@@ -57,6 +57,9 @@ SIGNATURES = {
     "tdssf_devox_scatter_add": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
     "tdssf_cels_workspace_bytes": (_sz, [_i64]),
     "tdssf_cels_fwd_bwd": (_i, [_p, _p, _p, _i64, _p, _f, _i, _p, C.POINTER(C.c_int64), _p, _p, _p, _p, _sz, _p]),
+    "tdssf_cels_count": (_i, [_p, _p, _i64, _i, _p, _p, _sz, _p]),
+    "tdssf_cels_fwd_bwd_counted": (_i, [_p, _p, _p, _i64, _p, _f, _i, _p, _p, _p, _p, _p, _sz, _p]),
+    "tdssf_cels_graph_stats": (None, [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "tdssf_cels_backward": (_i, [_p, _sz, _i64, _i64, _p, _p, _p, _p]),
     "tdssf_confusion": (_i, [_p, _p, _i64, _i, _p, _p]),
     "tdssf_compose_lidar2cam": (_i, [_p, _p, _p, _p, _i, _i, _p, _p, _p]),

@@ -64,6 +64,8 @@ def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
     if not params:
         return 0
     _, w = world()
+    if w == 1:
+        return sum(p.numel() for p in params)   # nothing to average
     dev = params[0].device
     shared = _shared_flat_grad(params)
     if shared is not None:
@@ -97,20 +99,20 @@ def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
 
 
 def _shared_flat_grad(params):
-    """The gradients of `params` as ONE 1-D fp32 tensor if they are back-to-back views of a single storage, else None."""
-    g0 = params[0].grad
-    if g0 is None or g0.dtype != torch.float32:
+    """The gradients of `params` as ONE 1-D fp32 tensor if they lie back to back in memory (tdssf.ops._flat_zero_grads hands
+    them out as views of one buffer, every size a multiple of four), else None."""
+    grads = [p.grad for p in params]
+    if any(g is None or g.dtype != torch.float32 or not g.is_contiguous() for g in grads):
         return None
-    base = g0.untyped_storage().data_ptr()
-    ptr = g0.data_ptr()
-    total = 0
-    for p in params:
-        g = p.grad
-        if (g is None or g.dtype != torch.float32 or not g.is_contiguous() or g.untyped_storage().data_ptr() != base
-                or g.data_ptr() != ptr + 4 * total):
+    ptr, total = grads[0].data_ptr(), 0
+    for g in grads:
+        if g.data_ptr() != ptr + 4 * total:
             return None
         total += g.numel()
-    return torch.empty(0, dtype=torch.float32, device=g0.device).set_(g0.untyped_storage(), g0.storage_offset(), (total,))
+    g0 = grads[0]
+    if g0.untyped_storage().nbytes() < 4 * (g0.storage_offset() + total):
+        return None
+    return g0.as_strided((total,), (1,))
 
 
 def max_over_ranks(value: float, device=None) -> float:

@@ -554,19 +554,24 @@ def sub_records(args, rank, world, dev, timer, peaks, peak_kind, sw, wd, packed,
         parallel.allreduce_mean_grads(params)
         return total
 
-    for _ in range(4):
+    for _ in range(10):   # the loss sequence is captured into a CUDA graph once its buffers repeat
         loss = train_step()
     ms, _, _, _ = timer.region(train_step, steps)
     step_ms = ms / steps
     counts = count_kernels(train_step) if rank == 0 else None
     kps = (counts or {}).get("kernels_per_step")
-    launches += (steps + 4 + 3) * (kps or 45)
+    launches += (steps + 10 + 3) * (kps or 45)
+    import ctypes as C
+    from tdssf import _lib
+    gs = [C.c_int64(), C.c_int64(), C.c_int64()]
+    _lib.lib.tdssf_cels_graph_stats(*[C.byref(g) for g in gs])
     tf = FLOPS_TRAIN * PER * V / (step_ms * 1e-3) / 1e12
     out["train"] = {
         "workload": f"BASELINE configs[2]: {PER} sweeps x {V} pts per GPU, fused forward (saving bf16 rows) + CE/Lovasz-Softmax + backward"
                     + (f" + all-reduce(mean) of the 132432 MLP gradients over NCCL x{world}" if world > 1 else " (no all-reduce at N=1)"),
         "value": world * PER * V / (step_ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": step_ms,
-        "loss": float(loss), "launches": counts,
+        "loss": float(loss.detach()), "launches": counts,
+        "cels_graph": {"replays": gs[0].value, "captures": gs[1].value, "plain_sequences": gs[2].value},
         "roofline": {"bound": "tensor", "achieved": tf, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": tf / peaks["bf16_tflops"],
                      "flops_per_point": FLOPS_TRAIN,
                      "loss_hbm": {"algorithmic_bytes_per_point": LOSS_BYTES_PER_POINT,

@@ -257,6 +257,23 @@ TDSSF_API int tdssf_cels_fwd_bwd(const float* logits, const int64_t* labels, con
                        float* out_scalars, int64_t* n_valid_host, int64_t* preds, int64_t* gt,
                        float* dlogits, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same computation without a host synchronisation inside the call, in two stages on one workspace:
+ *   tdssf_cels_count            flags + scan only; the number of surviving rows goes to n_valid_dev (device int32), from where
+ *                               the caller may start an asynchronous copy to the host
+ *   tdssf_cels_fwd_bwd_counted  everything else, with every grid sized for n_rows and the real bounds read from the counts
+ *                               in the workspace (same results as tdssf_cels_fwd_bwd).  A call that repeats the arguments of
+ *                               a recent one (a training loop) is captured once into a CUDA graph and replayed with one
+ *                               launch (TDSSF_CELS_GRAPH=0 disables).  preds / gt hold n_valid meaningful entries. */
+TDSSF_API int tdssf_cels_count(const int64_t* labels, const uint8_t* mask, int64_t n_rows, int ignore_index, int32_t* n_valid_dev,
+                               void* workspace, size_t workspace_bytes, void* stream);
+TDSSF_API int tdssf_cels_fwd_bwd_counted(const float* logits, const int64_t* labels, const uint8_t* mask,
+                                         int64_t n_rows, const float* class_w, float lambda_lovasz, int ignore_index,
+                                         float* out_scalars, int64_t* preds, int64_t* gt,
+                                         float* dlogits, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Counters of tdssf_cels_fwd_bwd_counted since the library was loaded: graph replays, graph captures, plain launch sequences. */
+TDSSF_API void tdssf_cels_graph_stats(int64_t* replays, int64_t* captures, int64_t* plain);
+
 /* Backward through the individual terms (the reference's three loss outputs are all differentiable, utils/losses.py:60-70):
  * dlogits = coef[0] * d ce / d logits + coef[1] * d lovasz / d logits, from the workspace a tdssf_cels_fwd_bwd call on the
  * same n_rows left behind (probabilities, Jaccard gradients, per-class counts; the caller keeps it alive and unmodified).

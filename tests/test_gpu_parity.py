@@ -477,3 +477,41 @@ def test_evaluation_loop_dropin(ops, capsys):
     assert got["overall_acc"] == want["overall_acc"]           # integer counters: exact
     for k in want:   # fp32 means of the same integer matrix, reduced on the device here and on the host there
         assert np.allclose(np.asarray(got[k], dtype=np.float64), np.asarray(want[k], dtype=np.float64), rtol=1e-6, atol=1e-9), k
+
+
+def test_cels_counted_graph_replay_equals_synchronous_call(ops):
+    """tdssf_cels_count + tdssf_cels_fwd_bwd_counted (no host synchronisation, grids sized for n_rows, CUDA-graph replay
+    when the arguments repeat) gives bit-identical scalars, predictions, labels and gradients to tdssf_cels_fwd_bwd on the
+    same buffers, for fresh data in every call (first call plain, second captured, later ones replayed), including a call
+    in which no row survives."""
+    import ctypes as C
+    from tdssf import _lib
+    from tdssf.ops import _ptr, _stream
+    lib = _lib.lib
+    n_rows = 9000
+    gen = torch.Generator().manual_seed(77)
+    x = torch.empty(n_rows, 16, device="cuda")
+    lab = torch.empty(n_rows, dtype=torch.int64, device="cuda")
+    mask = torch.empty(n_rows, dtype=torch.uint8, device="cuda")
+    cw = torch.tensor(synth.CLASS_WEIGHTS, device="cuda")
+    ws_bytes = lib.tdssf_cels_workspace_bytes(n_rows)
+    bufs = lambda: dict(work=torch.empty(ws_bytes, dtype=torch.uint8, device="cuda"), scal=torch.empty(4, device="cuda"),
+                        preds=torch.zeros(n_rows, dtype=torch.int64, device="cuda"), gt=torch.zeros(n_rows, dtype=torch.int64, device="cuda"),
+                        dlog=torch.empty(n_rows, 16, device="cuda"))
+    a, b = bufs(), bufs()
+    n_dev = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for call in range(5):
+        x.copy_(torch.randn(n_rows, 16, generator=gen) * 2)
+        lab.copy_(synth.make_labels(1, n_rows, gen).view(-1) if call != 3 else torch.zeros(n_rows, dtype=torch.int64))
+        mask.copy_((torch.rand(n_rows, generator=gen) > 0.1).to(torch.uint8))
+        nv = C.c_int64(0)
+        _lib.check(lib.tdssf_cels_fwd_bwd(_ptr(x), _ptr(lab), _ptr(mask), n_rows, _ptr(cw), 1.0, 0, _ptr(a["scal"]), C.byref(nv),
+                                          _ptr(a["preds"]), _ptr(a["gt"]), _ptr(a["dlog"]), _ptr(a["work"]), ws_bytes, _stream(x)))
+        _lib.check(lib.tdssf_cels_count(_ptr(lab), _ptr(mask), n_rows, 0, _ptr(n_dev), _ptr(b["work"]), ws_bytes, _stream(x)))
+        _lib.check(lib.tdssf_cels_fwd_bwd_counted(_ptr(x), _ptr(lab), _ptr(mask), n_rows, _ptr(cw), 1.0, 0, _ptr(b["scal"]),
+                                                  _ptr(b["preds"]), _ptr(b["gt"]), _ptr(b["dlog"]), _ptr(b["work"]), ws_bytes, _stream(x)))
+        n = int(nv.value)
+        assert int(n_dev.item()) == n and (n == 0) == (call == 3)
+        assert torch.equal(a["scal"].view(torch.int32), b["scal"].view(torch.int32)), (call, a["scal"], b["scal"])
+        assert torch.equal(a["preds"][:n], b["preds"][:n]) and torch.equal(a["gt"][:n], b["gt"][:n])
+        assert torch.equal(a["dlog"].view(torch.int32), b["dlog"].view(torch.int32)), call

@@ -37,3 +37,8 @@ for _ in range(100): step()
 torch.cuda.synchronize()
 pr.disable()
 st = pstats.Stats(pr); st.strip_dirs(); st.sort_stats("cumtime").print_stats(45)
+import ctypes as C
+from tdssf import _lib
+a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+_lib.lib.tdssf_cels_graph_stats(C.byref(a), C.byref(b), C.byref(c))
+print("cels graph: replays", a.value, "captures", b.value, "plain", c.value)

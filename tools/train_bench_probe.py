@@ -1,0 +1,36 @@
+"""Times bench.py's train sub-record loop alone and prints the CELS graph counters (debugging aid)."""
+import os, sys, time, json
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "3d-semantic-segmentation-fusion_b200")]
+import torch, ctypes as C
+from tdssf import synth, parallel, _lib
+from utils.fusion_model import FeatureFusionModel
+from utils.losses import CELSLoss
+import bench
+dev = torch.device("cuda")
+st = synth.make_sweeps(4, 34720, "dinov3", seed=3000)
+model = FeatureFusionModel(st.encoder, bench._IdentityPcd(), 64, 384, 16, device=dev).to(dev)
+model.load_state_dict(synth.make_mlp_weights(0), strict=True)
+crit = CELSLoss(weight=torch.tensor(synth.CLASS_WEIGHTS, device=dev), ignore_index=0, lamda_lovasz=1.0)
+d_tok, d_pts = st.tokens.to(dev), st.points.to(dev)
+d_feat = st.point_feat.to(dev).requires_grad_(True)
+d_lab, d_mask = st.labels.to(dev), st.mask.to(dev)
+params = list(model.mlp.parameters())
+def stats():
+    gs = [C.c_int64(), C.c_int64(), C.c_int64()]
+    _lib.lib.tdssf_cels_graph_stats(*[C.byref(g) for g in gs])
+    return [g.value for g in gs]
+def train_step(reduce=True):
+    for p in params: p.grad = None
+    d_feat.grad = None
+    scores = model(d_tok, d_feat, d_pts, None, st.image_sizes, st.K, st.Rt)
+    total = crit(scores, d_lab, d_mask)[0]
+    total.backward()
+    if reduce: parallel.allreduce_mean_grads(params)
+    return total
+for mode in (True, False):
+    for _ in range(6): train_step(mode)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(50): train_step(mode)
+    torch.cuda.synchronize()
+    print(json.dumps({"allreduce_call": mode, "step_us": (time.perf_counter() - t0) / 50 * 1e6, "graph_stats": stats()}))
