@@ -1115,52 +1115,7 @@ static int launch_as(const Params& p, cudaStream_t s) {
   cfg.numAttrs = 1;
   TDSSF_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
 #ifdef TDSSF_PROFILE
-  {  // experiment builds: dump the barrier-wait cycle counters of this launch (sums over waiting warps) and reset them
-    static int launches = 0;
-    unsigned long long h[64];
-    cudaStreamSynchronize(s);
-    cudaMemcpy(h, reinterpret_cast<unsigned long long*>(p.debug) + 2, sizeof(h), cudaMemcpyDeviceToHost);
-    static unsigned long long tr[16 * 32];
-    cudaMemcpy(tr, reinterpret_cast<unsigned long long*>(p.debug) + 128, sizeof(tr), cudaMemcpyDeviceToHost);
-    cudaMemset(p.debug, 0, 8192);
-    if (++launches == 8) {
-      const double ctas = 2.0 * clusters;
-      struct { int code; const char* name; double warps; } rows[] = {
-          {1, "mma wait own weights", 0.5}, {11, "mma wait peer weights", 0.5}, {2, "mma wait acc_free", 0.5},
-          {3, "mma wait a_full", 0.5}, {4, "mma wait h1_full", 0.5}, {5, "mma wait h2_full", 0.5},
-          {7, "epi wait acc1_full", kEpiWarps}, {8, "epi wait acc2_full", kEpiWarps}, {9, "epi wait acc3_full", 4},
-          {10, "prod wait a_empty", kProducerWarps}, {20, "prologue pass 1 (sum of groups)", kThreads / 32},
-          {21, "prologue pass 2", kThreads / 32}, {22, "prologue camera means", kThreads / 32},
-          {23, "prologue wait for slowest warp", kThreads / 32}};
-      fprintf(stderr, "[tdssf profile] gather=%d tok_bytes=%d n_pairs=%d clusters=%d (wait cycles per warp, averaged)\n",
-              (int)kGather, (int)sizeof(TokT), p.n_pairs, clusters);
-      for (auto& r : rows) fprintf(stderr, "  %-34s %12.0f\n", r.name, (double)h[r.code] / (r.warps * ctas));
-      const char* ev[16] = {"mma L1 start", "mma L1 issued", "mma H1 ready", "mma H2 ready", "epi acc1 full", "epi H1 done",
-                            "epi acc2 full", "epi H2 done", "epi acc3 full", "epi acc free", "prod tile start", "help start", "help end",
-                            "help pair issued", "help projected", "help pts loaded"};
-      fprintf(stderr, "  prologue %lld cycles; first L1 start %lld, last acc free %lld cycles after the prologue start (%d tiles)\n",
-              (long long)(tr[12 * 32] - tr[11 * 32]), (long long)(tr[0] - tr[11 * 32]),
-              (long long)(tr[9 * 32 + (p.n_pairs / clusters) - 1] - tr[11 * 32]), p.n_pairs / clusters);
-      {
-        const unsigned long long s0 = tr[13 * 32];
-        fprintf(stderr, "  slab trace, tiles 4-7 of cluster 5 rank 0 (producer warp 0 / MMA thread), cycles from the first entry\n"
-                        "  slab   prod:loads-awaited  slot-free  announced |  mma:seen-full  issued\n");
-        for (int i = 0; i < 28; ++i)
-          fprintf(stderr, "  %d.%d %18lld %10lld %10lld | %14lld %7lld\n", 4 + i / 7, i % 7, (long long)(tr[13 * 32 + i] - s0),
-                  (long long)(tr[14 * 32 + i] - s0), (long long)(tr[15 * 32 + i] - s0), (long long)(tr[11 * 32 + 1 + i] - s0),
-                  (long long)(tr[12 * 32 + 1 + i] - s0));
-      }
-      const unsigned long long t0 = tr[0 * 32 + 4];
-      fprintf(stderr, "  timeline of cluster 5 rank 0, cycles relative to 'mma L1 start' of tile 4\n  %-16s", "event");
-      for (int it = 4; it < 10; ++it) fprintf(stderr, " %9d", it);
-      fprintf(stderr, "\n");
-      for (int e = 0; e < 11; ++e) {
-        fprintf(stderr, "  %-16s", ev[e]);
-        for (int it = 4; it < 10; ++it) fprintf(stderr, " %9lld", (long long)(tr[e * 32 + it] - t0));
-        fprintf(stderr, "\n");
-      }
-    }
-  }
+#include "exp/mlp_tc_profile_dump.inc"
 #endif
   return TDSSF_OK;
 }
