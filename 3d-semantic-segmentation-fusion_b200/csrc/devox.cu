@@ -319,3 +319,42 @@ extern "C" int tdssf_devox_scatter_add(const float* dout, const int64_t* idx, in
   TDSSF_LAUNCH_CHECK();
   return TDSSF_OK;
 }
+
+// ---- tdssf_devox_nn_static: the grid-accelerated search for callers that cannot allocate device memory ------------
+// No counterpart in the reference.  The hash-grid workspace lives in a
+// file-scope device array (one instance per GPU that loads the library, held until exit) instead of a caller-owned
+// buffer.  In host code `g_devox_static_ws` is only a handle: its device address is fetched once per device with
+// cudaGetSymbolAddress while that device is current, and that address is what the kernels receive.  Every call shares
+// the array (the bucket heads, the unresolved-point counter and the origin rows are re-initialised by every call, so
+// nothing of the previous call is read); calls that overlap on the GPU race on it.
+constexpr size_t kDevoxStaticBytes = (size_t)TDSSF_DEVOX_NN_STATIC_BYTES;
+static __device__ __align__(256) unsigned char g_devox_static_ws[kDevoxStaticBytes];
+
+static int devox_static_ws(void** out) {
+  static void* base[tdssf::kMaxDevices] = {};
+  const int dev = tdssf::current_device();
+  if (!base[dev]) {
+    void* p = nullptr;
+    TDSSF_CUDA(cudaGetSymbolAddress(&p, g_devox_static_ws));
+    TDSSF_REQUIRE(p && ((uintptr_t)p & 255) == 0, "tdssf_devox_nn_static: bad address %p for the static workspace", p);
+    base[dev] = p;
+  }
+  *out = base[dev];
+  return TDSSF_OK;
+}
+
+extern "C" int tdssf_devox_nn_static(const float* pts, int64_t pts_stride, const float* vox, int64_t vox_stride,
+                                     int B, int P, int V, int64_t* idx, float cell, void* stream) {
+  using namespace tdssf;
+  TDSSF_REQUIRE(B >= 0 && P >= 0 && V >= 1, "tdssf_devox_nn_static: need B >= 0, P >= 0, V >= 1");
+  if (B == 0 || P == 0) return TDSSF_OK;
+  const size_t need = devox_ws_bytes(B, P, V);
+  TDSSF_REQUIRE(need <= kDevoxStaticBytes,
+                "tdssf_devox_nn_static: B=%d P=%d V=%d needs %zu workspace bytes, the static workspace holds %zu "
+                "(TDSSF_DEVOX_NN_STATIC_BYTES); use tdssf_devox_nn with a caller-owned workspace",
+                B, P, V, need, kDevoxStaticBytes);
+  void* ws = nullptr;
+  const int rc = devox_static_ws(&ws);
+  if (rc != TDSSF_OK) return rc;
+  return tdssf_devox_nn(pts, pts_stride, vox, vox_stride, B, P, V, idx, cell, ws, kDevoxStaticBytes, stream);
+}

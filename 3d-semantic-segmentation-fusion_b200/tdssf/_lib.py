@@ -53,6 +53,7 @@ SIGNATURES = {
     "tdssf_voxelize": (_i, [_p, _i64, _i, _i, _i, _d, _d, _p, _p, _p, _p, _p, _sz, _p]),
     "tdssf_devox_nn_workspace_bytes": (_sz, [_i, _i, _i]),
     "tdssf_devox_nn": (_i, [_p, _i64, _p, _i64, _i, _i, _i, _p, _f, _p, _sz, _p]),
+    "tdssf_devox_nn_static": (_i, [_p, _i64, _p, _i64, _i, _i, _i, _p, _f, _p]),
     "tdssf_devox_gather": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
     "tdssf_devox_scatter_add": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
     "tdssf_cels_workspace_bytes": (_sz, [_i64]),

@@ -208,6 +208,17 @@ TDSSF_API size_t tdssf_devox_nn_workspace_bytes(int B, int P, int V);
 TDSSF_API int tdssf_devox_nn(const float* pts, int64_t pts_stride, const float* vox, int64_t vox_stride,
                    int B, int P, int V, int64_t* idx, float cell, void* workspace, size_t workspace_bytes,
                    void* stream);
+/* tdssf_devox_nn (grid-accelerated path) for callers that cannot allocate device memory - code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  No counterpart in the reference.
+ * Same inputs, same indices, but the hash-grid workspace is a static device array of
+ * TDSSF_DEVOX_NN_STATIC_BYTES inside the library (one per GPU that loads it, held until exit); the call allocates
+ * nothing.  Limit: tdssf_devox_nn_workspace_bytes(B, P, V) <= TDSSF_DEVOX_NN_STATIC_BYTES (16 MiB: e.g. 8 sweeps of
+ * 34 720 raw points and voxels), beyond which it returns TDSSF_EINVAL with the sizes in tdssf_last_error().
+ * All calls on a device share that array: a call re-initialises what it reads, but two calls that overlap on the GPU
+ * (different streams without ordering, or two host threads) race - serialise them, or use tdssf_devox_nn. */
+#define TDSSF_DEVOX_NN_STATIC_BYTES (16u << 20)
+TDSSF_API int tdssf_devox_nn_static(const float* pts, int64_t pts_stride, const float* vox, int64_t vox_stride,
+                                    int B, int P, int V, int64_t* idx, float cell, void* stream);
 /* out[b,p,:] = scores[b,idx[b,p],:]   scores [B,V,C], out [B,P,C] */
 TDSSF_API int tdssf_devox_gather(const float* scores, const int64_t* idx, int B, int P, int V, int C,
                        float* out, void* stream);
