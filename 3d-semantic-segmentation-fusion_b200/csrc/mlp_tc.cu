@@ -68,10 +68,18 @@ constexpr int kOffW2 = kOffW1 + kSlabs1 * kW1Slab;          // 114688
 constexpr int kOffW3 = kOffW2 + kSlabs2 * kW2Slab;          // 131072
 constexpr int kWeightBytes = kOffW3 + kW3Slab;              // 133120 per CTA rank
 constexpr int kBiasFloats = kN1 + kN2 + kClasses;           // 336
-constexpr int kOffRing = kWeightBytes;                      // 1024-aligned
+// The biases ride on the tensor core: every accumulator starts as ones[128 x 16] @ biasrows[N x 16]^T, one extra K = 16
+// MMA per layer, instead of 336 shared-memory loads and 208 additions per point row in the epilogues (which queue behind
+// the producers' gather in the load/store unit).  K slot 0 carries bf16(b), slot 1 bf16(b - bf16(b)): the sum is b to
+// 2^-17.  Both operands are K-major without swizzle: element (row, k) at (row/8)*256 + (k/8)*128 + (row%8)*16 + (k%8)*2.
+constexpr int kOffBiasB1 = kWeightBytes;                    // [128 rows][16]  4 KB
+constexpr int kOffBiasB2 = kOffBiasB1 + (kN1 / 2) * 32;     // [32 rows][16]   1 KB
+constexpr int kOffBiasB3 = kOffBiasB2 + (kN2 / 2) * 32;     // [16 rows][16]   512 B
+constexpr int kImageBytes = (kOffBiasB3 + (kN3 / 2) * 32 + 1023) & ~1023;   // 139264 per CTA rank, what the bulk copy brings in
+constexpr int kOffRing = kImageBytes;                       // 1024-aligned
 constexpr int kASlab = kTileM * 128;                        // 16 KB
-constexpr int kOffBias = kOffRing + kStages * kASlab;       // 215040
-constexpr int kOffBar = kOffBias + ((kBiasFloats * 4 + 15) & ~15);
+constexpr int kOffOnes = kOffRing + kStages * kASlab;       // A operand of the bias MMAs: [128 rows][16], ones in K slots 0 and 1
+constexpr int kOffBar = kOffOnes + kTileM * 32;
 constexpr int kNumBars = 2 * kStages + 2 + 6 * 2;
 constexpr int kOffTmemPtr = kOffBar + kNumBars * 8;
 constexpr int kOffGroupCtr = kOffTmemPtr + 8;              // prologue: next unclaimed group of 32 points
@@ -79,10 +87,10 @@ constexpr int kSmemBytes = kOffTmemPtr + 16;
 constexpr int kCalFloats = 24;                              // per camera: rows 0..2 of lidar->camera, K, 3 floats of padding
 constexpr int kCalStageFloats = kStages * kASlab / 4;       // the idle A ring holds the calibration during the prologue
 static_assert(kSmemBytes + 1024 <= 232448, "shared memory budget exceeded");
-static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0, "slab alignment");
+static_assert(kOffRing % 1024 == 0 && kOffW2 % 1024 == 0 && kOffW3 % 1024 == 0 && kImageBytes % 16 == 0, "slab alignment");
 static_assert(32 * (kEpiWarps * kRegsEpi + kAuxWarps * kRegsAux + kProducerWarps * kRegsProd) <= (65536 / kThreads / 8 * 8) * kThreads, "register budget");
 
-constexpr size_t kPackBytes = 2 * (size_t)kWeightBytes + kBiasFloats * 4 + 64;
+constexpr size_t kPackBytes = 2 * (size_t)kImageBytes + 64;
 
 // barrier indices
 enum {
@@ -169,6 +177,9 @@ __device__ __forceinline__ void wait_bar_poll(uint32_t bar, uint32_t parity, uns
   if (ptx::mbar_test_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!ptx::mbar_test_wait(bar, parity)) {
+#ifdef TDSSF_MMA_NAP
+    __nanosleep(TDSSF_MMA_NAP);
+#endif
     if (clock64() - t0 > 4000000000LL) {
       if (debug) atomicExch(debug, (unsigned)code | 0x80000000u);
       __trap();
@@ -568,7 +579,6 @@ fused_mlp_kernel(const Params p) {
   auto tile_row0 = [&](int it) {
     return (((int64_t)ptx::cluster_id_x() + (int64_t)it * ptx::num_clusters_x()) * 2 + rank) * kTileM;
   };
-  float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + kOffTmemPtr);
 
   // ---- one-time setup ------------------------------------------------------------------------------
@@ -599,9 +609,13 @@ fused_mlp_kernel(const Params p) {
     for (int i = threadIdx.x; i < 2 * p.B; i += kThreads) s_cal[n_cams * kCalFloats + i] = __ldg(p.img_hw + i);
     if (threadIdx.x == 0) *reinterpret_cast<volatile uint32_t*>(smem + kOffGroupCtr) = 0u;
   }
-  {  // biases (shared by both ranks) live after the two weight images
-    const float* gb = reinterpret_cast<const float*>(p.packed + 2 * (size_t)kWeightBytes);
-    for (int i = threadIdx.x; i < kBiasFloats; i += kThreads) s_bias[i] = __ldg(gb + i);
+  {  // A operand of the bias MMAs: 1.0 in K slots 0 and 1 of every row (written once, read by the tensor core only)
+    uint32_t* ones = reinterpret_cast<uint32_t*>(smem + kOffOnes);
+    for (int i = threadIdx.x; i < kTileM * 8; i += kThreads) {
+      const int wi = i & 63;                                       // word inside a group of 8 rows (256 bytes)
+      ones[i] = (wi < 32 && (wi & 3) == 0) ? 0x3f803f80u : 0u;     // first word of a row's K 0..7 chunk: bf16 {1, 1}
+    }
+    ptx::fence_proxy_async_smem();
   }
   if (warp == kMmaWarp) {
     ptx::tmem_alloc_2cta(sbase + kOffTmemPtr, 512);
@@ -614,10 +628,10 @@ fused_mlp_kernel(const Params p) {
   const uint32_t tmem = *s_tmem;
 
   if (warp == kMmaWarp && lane == 0) {  // the weights land while the prologue runs
-    const uint8_t* src = p.packed + (size_t)rank * kWeightBytes;
-    ptx::mbar_expect_tx(bar(kBarWFull), kWeightBytes);
-    for (int off = 0; off < kWeightBytes; off += 16384) {
-      const int n = min(16384, kWeightBytes - off);
+    const uint8_t* src = p.packed + (size_t)rank * kImageBytes;
+    ptx::mbar_expect_tx(bar(kBarWFull), kImageBytes);
+    for (int off = 0; off < kImageBytes; off += 16384) {
+      const int n = min(16384, kImageBytes - off);
       ptx::bulk_g2s(sbase + kOffW1 + off, src + off, n, bar(kBarWFull));
     }
   }
@@ -641,14 +655,11 @@ fused_mlp_kernel(const Params p) {
     const int row_in_tile = (int)(q4 * 32u) + lane;
     const uint32_t leader_h1 = ptx::mapa(bar(kBarH1Full), 0), leader_h2 = ptx::mapa(bar(kBarH2Full), 0),
                    leader_free = ptx::mapa(bar(kBarAccFree), 0);
-    // bias + ReLU + bf16 of 16 accumulator columns
-    auto act16 = [&](const uint32_t (&v)[16], const float* bias, uint32_t (&h)[8]) {
+    // ReLU + bf16 of 16 accumulator columns (the bias is already in the accumulator: bias MMA)
+    auto act16 = [&](const uint32_t (&v)[16], uint32_t (&h)[8]) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float4 bq = *reinterpret_cast<const float4*>(bias + 4 * j);
-        h[2 * j] = pack_bf16(fmaxf(__uint_as_float(v[4 * j]) + bq.x, 0.f), fmaxf(__uint_as_float(v[4 * j + 1]) + bq.y, 0.f));
-        h[2 * j + 1] = pack_bf16(fmaxf(__uint_as_float(v[4 * j + 2]) + bq.z, 0.f), fmaxf(__uint_as_float(v[4 * j + 3]) + bq.w, 0.f));
-      }
+      for (int j = 0; j < 8; ++j)
+        h[j] = pack_bf16(fmaxf(__uint_as_float(v[2 * j]), 0.f), fmaxf(__uint_as_float(v[2 * j + 1]), 0.f));
     };
     for (int it = 0; it < n_iters; ++it) {
       const uint32_t buf = it & 1, par = (it >> 1) & 1;
@@ -663,13 +674,12 @@ fused_mlp_kernel(const Params p) {
       {
         uint32_t va[16], vb[16], h[8];
         const uint32_t src = tb + ch * 128;
-        const float* bias = s_bias + ch * 128;
         ptx::tmem_ld16(src, va);
 #pragma unroll
         for (int c = 0; c < 8; c += 2) {
           ptx::tmem_wait_ld();
           ptx::tmem_ld16(src + (c + 1) * 16, vb);
-          act16(va, bias + c * 16, h);
+          act16(va, h);
           ptx::tmem_st8(src + c * 8, h);
           if (save_h1) {
             uint4* d = reinterpret_cast<uint4*>(p.h1_out + row * kN1 + ch * 128 + c * 16);
@@ -678,7 +688,7 @@ fused_mlp_kernel(const Params p) {
           }
           ptx::tmem_wait_ld();
           if (c + 2 < 8) ptx::tmem_ld16(src + (c + 2) * 16, va);
-          act16(vb, bias + (c + 1) * 16, h);
+          act16(vb, h);
           ptx::tmem_st8(src + (c + 1) * 8, h);
           if (save_h1) {
             uint4* d = reinterpret_cast<uint4*>(p.h1_out + row * kN1 + ch * 128 + (c + 1) * 16);
@@ -702,18 +712,17 @@ fused_mlp_kernel(const Params p) {
       {
         uint32_t va[16], vb[16], h[8];
         const uint32_t src = tb + 64 + ch * 32, dst = tb + 192 + ch * 16;
-        const float* bias = s_bias + kN1 + ch * 32;
         ptx::tmem_ld16(src, va);
         ptx::tmem_ld16(src + 16, vb);
         ptx::tmem_wait_ld();
-        act16(va, bias, h);
+        act16(va, h);
         ptx::tmem_st8(dst, h);
         if (save_h2) {
           uint4* d = reinterpret_cast<uint4*>(p.h2_out + row * kN2 + ch * 32);
           d[0] = make_uint4(h[0], h[1], h[2], h[3]);
           d[1] = make_uint4(h[4], h[5], h[6], h[7]);
         }
-        act16(vb, bias + 16, h);
+        act16(vb, h);
         ptx::tmem_st8(dst + 8, h);
         if (save_h2) {
           uint4* d = reinterpret_cast<uint4*>(p.h2_out + row * kN2 + ch * 32 + 16);
@@ -748,16 +757,22 @@ fused_mlp_kernel(const Params p) {
           bool nan_seen = false;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float4 bq = *reinterpret_cast<const float4*>(s_bias + kN1 + kN2 + 4 * j);
-            const float4 o = make_float4(__uint_as_float(v[4 * j]) + bq.x, __uint_as_float(v[4 * j + 1]) + bq.y,
-                                         __uint_as_float(v[4 * j + 2]) + bq.z, __uint_as_float(v[4 * j + 3]) + bq.w);
-            dst[j] = o;
+            const float4 o = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                         __uint_as_float(v[4 * j + 3]));
             const float e[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
             for (int k = 0; k < 4; ++k) {  // torch.argmax: first maximum, a NaN counts as the maximum
               const bool is_nan = e[k] != e[k];
               if (!nan_seen && (is_nan || e[k] > best || (j == 0 && k == 0))) { best = e[k]; arg = 4 * j + k; nan_seen = is_nan; }
             }
+          }
+          // 64 bytes per row as two 256-bit stores (half the store instructions and L1 wavefronts of four 128-bit ones)
+          if ((reinterpret_cast<uintptr_t>(p.logits) & 31) == 0) {
+            ptx::stg256(dst, v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+            ptx::stg256(dst + 2, v[8], v[9], v[10], v[11], v[12], v[13], v[14], v[15]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
           }
           if (p.preds_out) p.preds_out[row] = arg + 1;
         }
@@ -766,6 +781,7 @@ fused_mlp_kernel(const Params p) {
   } else if (warp < kProdWarp0) {
     if (kRegsAux < 96) ptx::setmaxnreg_dec<kRegsAux>(); else ptx::setmaxnreg_inc<kRegsAux>();
     constexpr uint32_t kI1 = ptx::idesc_bf16(256, kN1), kI2 = ptx::idesc_bf16(256, kN2), kI3 = ptx::idesc_bf16(256, kN3);
+    const uint64_t ones_desc = ptx::smem_desc_nosw(sbase + kOffOnes, 128, 256);
     if (warp == kMmaWarp) {
       // =============================== weights + layer-1 MMA issue ===================================
       // tcgen05.mma issue is paced by the tensor pipe (the issuing thread blocks while the previous MMA starts), so the
@@ -781,6 +797,7 @@ fused_mlp_kernel(const Params p) {
           if (it >= 2) wait_bar_poll(bar(kBarAccFree + buf), ((it >> 1) - 1) & 1, p.debug, 2);
           ptx::tc_fence_after();
           TRACE(p.debug, 0, it);
+          ptx::umma_ss_2cta(tmem + buf * 256, ones_desc, ptx::smem_desc_nosw(sbase + kOffBiasB1, 128, 256), kI1, 0);  // acc1 = b1
 #pragma unroll 1
           for (int s = 0; s < kSlabs1; ++s) {
             wait_bar_poll(bar(kBarAFull + stage), phase, p.debug, 3);
@@ -791,7 +808,7 @@ fused_mlp_kernel(const Params p) {
               const uint64_t ad = ptx::smem_desc_sw128(sbase + kOffRing + stage * kASlab + kk * 32);
               const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW1 + s * kW1Slab + kk * 32);
 #ifndef TDSSF_EXP_NOMMA  // (timing experiment: layer 1 not issued)
-              ptx::umma_ss_2cta(tmem + buf * 256, ad, bd, kI1, (s | kk) != 0);
+              ptx::umma_ss_2cta(tmem + buf * 256, ad, bd, kI1, 1);
 #else
               (void)ad; (void)bd;
 #endif
@@ -821,12 +838,13 @@ fused_mlp_kernel(const Params p) {
           wait_bar_poll(bar(kBarH1Full + buf), par, p.debug, 4);
           ptx::tc_fence_after();
           TRACE(p.debug, 2, it);
-          // layer 2: A = H1 (TMEM cols [0,64) and [128,192) of the buffer), B = W2, D = cols [64,128)
+          // layer 2: A = H1 (TMEM cols [0,64) and [128,192) of the buffer), B = W2, D = cols [64,128), starting from b2
+          ptx::umma_ss_2cta(tb + 64, ones_desc, ptx::smem_desc_nosw(sbase + kOffBiasB2, 128, 256), kI2, 0);
 #pragma unroll
           for (int k = 0; k < kN1 / 16; ++k) {
             const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
 #ifndef TDSSF_EXP_NOL23  // (timing experiment: layers 2 and 3 not issued)
-            ptx::umma_ts_2cta(tb + 64, tb + (k < 8 ? k * 8 : 128 + (k - 8) * 8), bd, kI2, k != 0);
+            ptx::umma_ts_2cta(tb + 64, tb + (k < 8 ? k * 8 : 128 + (k - 8) * 8), bd, kI2, 1);
 #else
             (void)bd;
 #endif
@@ -835,12 +853,13 @@ fused_mlp_kernel(const Params p) {
           wait_bar_poll(bar(kBarH2Full + buf), par, p.debug, 5);
           ptx::tc_fence_after();
           TRACE(p.debug, 3, it);
-          // layer 3: A = H2 (cols [192,224)), B = W3, D = cols [224,256)
+          // layer 3: A = H2 (cols [192,224)), B = W3, D = cols [224,256), starting from b3
+          ptx::umma_ss_2cta(tb + 224, ones_desc, ptx::smem_desc_nosw(sbase + kOffBiasB3, 128, 256), kI3, 0);
 #pragma unroll
           for (int k = 0; k < kN2 / 16; ++k) {
             const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
 #ifndef TDSSF_EXP_NOL23
-            ptx::umma_ts_2cta(tb + 224, tb + 192 + k * 8, bd, kI3, k != 0);
+            ptx::umma_ts_2cta(tb + 224, tb + 192 + k * 8, bd, kI3, 1);
 #else
             (void)bd;
 #endif
@@ -1081,12 +1100,25 @@ __global__ void pack_weights_kernel(const float* __restrict__ W1, const float* _
     const int k = slab * kSlabK + chunk * 8 + within;
     const int n = rank * rows_cta + r;
     const float v = (n < n_valid) ? W[(int64_t)n * ld + k] : 0.f;
-    reinterpret_cast<__nv_bfloat16*>(out + (size_t)rank * kWeightBytes)[byte / 2] = __float2bfloat16_rn(v);
+    reinterpret_cast<__nv_bfloat16*>(out + (size_t)rank * kImageBytes)[byte / 2] = __float2bfloat16_rn(v);
   }
-  if (blockIdx.x == 0) {
-    float* gb = reinterpret_cast<float*>(out + 2 * (size_t)kWeightBytes);
-    for (int i = threadIdx.x; i < kBiasFloats; i += blockDim.x)
-      gb[i] = i < kN1 ? b1[i] : (i < kN1 + kN2 ? b2[i - kN1] : b3[i - kN1 - kN2]);
+  // B operands of the bias MMAs: per layer [rows of this rank][16], K slot 0 = bf16(b), slot 1 = bf16(b - slot 0), rest 0
+  const int bias_elems = (kImageBytes - kWeightBytes) / 2;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 2 * bias_elems; e += gridDim.x * blockDim.x) {
+    const int rank = e / bias_elems;
+    const int byte = kWeightBytes + (e % bias_elems) * 2;
+    const float* b; int rows_cta, off, n_valid;
+    if (byte < kOffBiasB2) { b = b1; rows_cta = kN1 / 2; off = byte - kOffBiasB1; n_valid = kN1; }
+    else if (byte < kOffBiasB3) { b = b2; rows_cta = kN2 / 2; off = byte - kOffBiasB2; n_valid = kN2; }
+    else { b = b3; rows_cta = kN3 / 2; off = byte - kOffBiasB3; n_valid = kClasses; }
+    const int r = (off / 256) * 8 + (off % 128) / 16, k = ((off % 256) / 128) * 8 + (off % 16) / 2;
+    const int n = rank * rows_cta + r;
+    float v = 0.f;
+    if (r < rows_cta && n < n_valid && k < 2) {
+      const float hi = __bfloat162float(__float2bfloat16_rn(b[n]));
+      v = k == 0 ? hi : b[n] - hi;
+    }
+    reinterpret_cast<__nv_bfloat16*>(out + (size_t)rank * kImageBytes)[byte / 2] = __float2bfloat16_rn(v);
   }
 }
 
