@@ -265,9 +265,6 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
           ptx::tmem_wait_ld();
           if (half == 0) ptx::tmem_ld16(tl + (c + 1) * 16, vb);
           else if (c + 2 < 16) ptx::tmem_ld16(tl + (c + 2) * 16, va);
-#ifdef TDSSF_CH_NOE1   // (timing experiment: TMEM loads only)
-          if (p.N < 0)
-#endif
 #pragma unroll
           for (int k = 0; k < 2; ++k) {
             const int q = (cc & 3) * 2 + k;
@@ -308,16 +305,12 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
           if (lane == 0) ptx::mbar_arrive_local(bar(kAccxFree));
           __syncwarp();
         }
-#ifndef TDSSF_CH_NODX   // (timing experiment: no dx_pt stores)
         if (store) {   // a row per thread: 32-byte stores, every lane in its own line
           ptx::stg256(dst + half * 8, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], x0[6], x0[7]);
           ptx::stg256(dst + half * 8 + 2, x0[8], x0[9], x0[10], x0[11], x0[12], x0[13], x0[14], x0[15]);
           ptx::stg256(dst + half * 8 + 4, x1[0], x1[1], x1[2], x1[3], x1[4], x1[5], x1[6], x1[7]);
           ptx::stg256(dst + half * 8 + 6, x1[8], x1[9], x1[10], x1[11], x1[12], x1[13], x1[14], x1[15]);
         }
-#else
-        (void)store; (void)dst;
-#endif
       }
       if (warp == 0) CH_TRACE(3, it);
     }
@@ -455,9 +448,6 @@ dgrad_chain_kernel(const __grid_constant__ CUtensorMap tm_h1, const Params p) {
     for (int e = 0; e < 8; ++e) s1[e] = s2[e] = 0.f;
     // rows [r_lo, r_hi) of a [128 x 64] slab: four rows per instruction (eight lanes x 16 bytes each)
     auto drain = [&](uint32_t slab, uint16_t* out, int ld, int col0, int64_t row0, int r_lo, int r_hi, float (&acc)[8]) {
-#ifdef TDSSF_CH_NODRAIN   // (timing experiment: helpers only run the barrier protocol)
-      if (p.N >= 0) return;
-#endif
       for (int r4 = r_lo + rg; r4 < r_hi; r4 += 16) {   // four loads in flight, then their sums and stores
         uint4 v[4];
 #pragma unroll
@@ -600,9 +590,6 @@ __device__ __forceinline__ void run(const CUtensorMap& tm_dh1, const CUtensorMap
           const uint32_t acc = (i | kk) != 0;
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
-#ifdef TDSSF_WG_NOMMA   // (timing experiment: loads only)
-            continue;
-#endif
             const uint64_t a = ptx::smem_desc_sw128_ex(base + (2 * h) * kSlab + koff, kSlab, 1024);
             if (!kB) {
               ptx::umma_ss_1cta(tmem + h * 256, a, ptx::smem_desc_sw128_ex(base + 4 * kSlab + koff, kSlab, 1024), kI256, acc);
@@ -628,9 +615,6 @@ __device__ __forceinline__ void run(const CUtensorMap& tm_dh1, const CUtensorMap
     float* buf = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 36);   // the ring is idle once `done` completed
     float* out = p.partials + (size_t)blockIdx.x * kPartialFloats + (size_t)(qd * 32) * 512;
     const uint32_t tl = tmem + (((uint32_t)qd * 32u) << 16);
-#ifdef TDSSF_WG_NOEPI   // (timing experiment: no partial written)
-    if (p.N >= 0) return;
-#endif
     for (int c0 = ch * 256; c0 < ch * 256 + 256; c0 += 32) {
       uint32_t va[16], vb[16];
       if (n_my > 0) {

@@ -50,14 +50,8 @@ constexpr int kThreads = 32 * (kEpiWarps + kAuxWarps + kProducerWarps);  // 512
 constexpr int kRowsPerWarp = kTileM / kProducerWarps;                    // 16
 constexpr int kSteps = kRowsPerWarp / 4;                                 // 4 rows per quarter-warp
 // launch: 640 threads x 96 registers = 61440, redistributed over the roles (all of it is used)
-#ifndef TDSSF_SETS
-#define TDSSF_SETS 3  // producer register sets: slabs whose loads are in flight while one is converted, plus one
-#endif
-#if TDSSF_SETS == 3
+// three producer register sets: the loads of two slabs in flight while a third is converted (two sets: 3-5 % slower)
 constexpr int kRegsEpi = 72, kRegsAux = 64, kRegsProd = 136;   // 256*72 + 128*64 + 256*136 = 61440
-#else
-constexpr int kRegsEpi = 72, kRegsAux = 64, kRegsProd = 112;   // 256*72 + 128*64 + 256*112 = 55296
-#endif
 
 // per-CTA shared-memory image (bytes)
 constexpr int kW1Slab = (kN1 / 2) * 128;   // 128 rows x 128 B = 16 KB
@@ -150,11 +144,7 @@ struct Params {
 #define TRACE(dbg, ev, it)
 #endif
 
-#ifdef TDSSF_SPIN
-#define TDSSF_WAIT_PROBE ptx::mbar_test_wait   // busy polling: reacts within a few tens of cycles
-#else
 #define TDSSF_WAIT_PROBE ptx::mbar_try_wait    // suspends the warp until the phase completes (or the time hint expires)
-#endif
 __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* debug, int code) {
   if (TDSSF_WAIT_PROBE(bar, parity)) return;
   const long long t0 = clock64();
@@ -171,15 +161,9 @@ __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned
 
 // busy-polling wait for the single MMA-issuing threads: reacts within a few tens of cycles
 __device__ __forceinline__ void wait_bar_poll(uint32_t bar, uint32_t parity, unsigned int* debug, int code) {
-#ifdef TDSSF_MMA_SLEEPS
-  wait_bar(bar, parity, debug, code);
-#else
   if (ptx::mbar_test_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!ptx::mbar_test_wait(bar, parity)) {
-#ifdef TDSSF_MMA_NAP
-    __nanosleep(TDSSF_MMA_NAP);
-#endif
     if (clock64() - t0 > 4000000000LL) {
       if (debug) atomicExch(debug, (unsigned)code | 0x80000000u);
       __trap();
@@ -187,7 +171,6 @@ __device__ __forceinline__ void wait_bar_poll(uint32_t bar, uint32_t parity, uns
   }
 #ifdef TDSSF_PROFILE
   PROF_ADD(debug, code, t0);
-#endif
 #endif
 }
 
@@ -203,18 +186,10 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // consumer so that the request stays in flight.
 __device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 // coherent 16-byte load: the scratch rows of multi-camera points are written by this CTA during the kernel
-#ifndef TDSSF_LDMODE
-#define TDSSF_LDMODE 0  // experiment: 0 ld.global (L1 allocate)  1 ld.global.cg (L2 only)  2 ld.global.L1::no_allocate
-#endif
 __device__ __forceinline__ uint4 ldg16c(const void* p) {
   uint4 r;
-#if TDSSF_LDMODE == 1
-  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-#elif TDSSF_LDMODE == 2
-  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-#else
+  // L1-allocating: L2-only (.cg) and L1::no_allocate loads were measured 14 % slower
   asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-#endif
   return r;
 }
 struct Raw8 { uint4 lo, hi; };
@@ -670,7 +645,6 @@ fused_mlp_kernel(const Params p) {
       wait_bar(bar(kBarAcc1Full + buf), par, p.debug, 7);
       ptx::tc_fence_after();
       if (warp == 0) TRACE(p.debug, 4, it);
-#ifndef TDSSF_EXP_NOEPI  // (timing experiment: the epilogue only runs the barrier protocol)
       {
         uint32_t va[16], vb[16], h[8];
         const uint32_t src = tb + ch * 128;
@@ -697,7 +671,6 @@ fused_mlp_kernel(const Params p) {
           }
         }
       }
-#endif
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
@@ -708,7 +681,6 @@ fused_mlp_kernel(const Params p) {
       wait_bar(bar(kBarAcc2Full + buf), par, p.debug, 8);
       ptx::tc_fence_after();
       if (warp == 0) TRACE(p.debug, 6, it);
-#ifndef TDSSF_EXP_NOEPI
       {
         uint32_t va[16], vb[16], h[8];
         const uint32_t src = tb + 64 + ch * 32, dst = tb + 192 + ch * 16;
@@ -730,7 +702,6 @@ fused_mlp_kernel(const Params p) {
           d[1] = make_uint4(h[4], h[5], h[6], h[7]);
         }
       }
-#endif
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
@@ -807,11 +778,7 @@ fused_mlp_kernel(const Params p) {
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t ad = ptx::smem_desc_sw128(sbase + kOffRing + stage * kASlab + kk * 32);
               const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW1 + s * kW1Slab + kk * 32);
-#ifndef TDSSF_EXP_NOMMA  // (timing experiment: layer 1 not issued)
               ptx::umma_ss_2cta(tmem + buf * 256, ad, bd, kI1, 1);
-#else
-              (void)ad; (void)bd;
-#endif
             }
             ptx::umma_commit_2cta(bar(kBarAEmpty + stage), 3);
             if (it >= 4 && it < 8) TRACE(p.debug, 12, 1 + (it - 4) * 7 + s);   // its MMAs and commit issued
@@ -843,11 +810,7 @@ fused_mlp_kernel(const Params p) {
 #pragma unroll
           for (int k = 0; k < kN1 / 16; ++k) {
             const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW2 + (k >> 2) * kW2Slab + (k & 3) * 32);
-#ifndef TDSSF_EXP_NOL23  // (timing experiment: layers 2 and 3 not issued)
             ptx::umma_ts_2cta(tb + 64, tb + (k < 8 ? k * 8 : 128 + (k - 8) * 8), bd, kI2, 1);
-#else
-            (void)bd;
-#endif
           }
           ptx::umma_commit_2cta(bar(kBarAcc2Full + buf), 3);
           wait_bar_poll(bar(kBarH2Full + buf), par, p.debug, 5);
@@ -858,11 +821,7 @@ fused_mlp_kernel(const Params p) {
 #pragma unroll
           for (int k = 0; k < kN2 / 16; ++k) {
             const uint64_t bd = ptx::smem_desc_sw128(sbase + kOffW3 + k * 32);
-#ifndef TDSSF_EXP_NOL23
             ptx::umma_ts_2cta(tb + 224, tb + 192 + k * 8, bd, kI3, 1);
-#else
-            (void)bd;
-#endif
           }
           ptx::umma_commit_2cta(bar(kBarAcc3Full + buf), 3);
         }
@@ -933,9 +892,6 @@ fused_mlp_kernel(const Params p) {
     };
     auto issue_one = [&](auto S_, int it, int st, Set& n) {
       constexpr int S = decltype(S_)::value;
-#if defined(TDSSF_EXP_NOPROD) || defined(TDSSF_EXP_NOLOAD)  // (timing experiments: no global loads)
-      return;
-#endif
       if (S == 0) {  // point features
         const int64_t row = tile_row0(it) + pw * kRowsPerWarp + row_of(st, quarter);
         const char* px = row < p.N ? reinterpret_cast<const char*>(p.x_pt) + row * (kCp * 4) + ql * 16 : zero_row;
@@ -958,10 +914,6 @@ fused_mlp_kernel(const Params p) {
     auto consume_one = [&](auto S_, int it, int st, const Set& c, uint32_t slab_off) {
       constexpr int S = decltype(S_)::value;
       constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
-#if defined(TDSSF_EXP_NOPROD) || defined(TDSSF_EXP_NOSTORE)  // (timing experiments: no conversion, no stores)
-      (void)slab_off;
-      return;
-#endif
       float acc[8];
       // training: the bf16 input row also goes to HBM for the weight gradient (x_out), 64 contiguous bytes per quarter-warp
       const int64_t row = tile_row0(it) + pw * kRowsPerWarp + row_of(st, quarter);
@@ -990,13 +942,6 @@ fused_mlp_kernel(const Params p) {
     auto step_fused = [&](auto S_, int it, const Set& cur, auto S2_, int it2, Set& nxt) {
       constexpr int S = decltype(S_)::value;
       if (it2 < n_iters) issue(S2_, it2, nxt);
-#ifdef TDSSF_XPT_PREFETCH  // (experiment) the next tile's point features, one contiguous 32 KB block, towards L2
-      if (S == 2 && pw == 0 && lane == 0 && it + 1 < n_iters) {
-        const int64_t r0 = tile_row0(it + 1);
-        if (r0 + kTileM <= p.N)
-          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.x_pt + r0 * kCp), "r"(kTileM * kCp * 4) : "memory");
-      }
-#endif
       if (S == 0 && pw == 0) TRACE(p.debug, 10, it);
       if (pw == 0 && it >= 4 && it < 8) TRACE(p.debug, 13, (it - 4) * 7 + S);   // slab trace: loads issued
       wait_bar(bar(kBarAEmpty + stage), phase ^ 1, p.debug, 10);
@@ -1017,7 +962,6 @@ fused_mlp_kernel(const Params p) {
     // Item stream (tile, slab): item i is converted out of register set i % kSets after the loads of item
     // i + kSets - 1 went into the set that item i - 1 has just left.  7 slabs per tile, so the rotation closes after
     // kSets tiles.
-#if TDSSF_SETS == 3
     Set R0, R1, R2;
     auto step = [&](auto S_, int it, Set& cur, Set& nxt2) {
       constexpr int S = decltype(S_)::value;
@@ -1044,32 +988,6 @@ fused_mlp_kernel(const Params p) {
         if (it + 2 < n_iters) tile(it + 2, R2, R0, R1);
       }
     }
-#else
-    Set R0, R1;
-    auto step = [&](auto S_, int it, Set& cur, Set& nxt) {
-      constexpr int S = decltype(S_)::value;
-      constexpr int S1 = (S + 1) % kSlabs1;
-      const int it1 = it + (S + 1 >= kSlabs1 ? 1 : 0);
-      step_fused(S_, it, cur, std::integral_constant<int, S1>{}, it1, nxt);
-    };
-    auto tile = [&](int it, Set& x, Set& y) {  // slab 0 in x
-      step(std::integral_constant<int, 0>{}, it, x, y);
-      step(std::integral_constant<int, 1>{}, it, y, x);
-      step(std::integral_constant<int, 2>{}, it, x, y);
-      step(std::integral_constant<int, 3>{}, it, y, x);
-      step(std::integral_constant<int, 4>{}, it, x, y);
-      step(std::integral_constant<int, 5>{}, it, y, x);
-      step(std::integral_constant<int, 6>{}, it, x, y);   // loads slab 0 of the next tile into y
-    };
-    if (n_iters > 0) {
-      issue(std::integral_constant<int, 0>{}, 0, R0);
-#pragma unroll 1
-      for (int it = 0; it < n_iters; it += 2) {
-        tile(it, R0, R1);
-        if (it + 1 < n_iters) tile(it + 1, R1, R0);
-      }
-    }
-#endif
   }
 
   // ---- teardown ----------------------------------------------------------------------------------------

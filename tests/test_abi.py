@@ -73,5 +73,5 @@ def test_error_convention(lib_path):
     assert rc == _lib.EINVAL and "tdssf_confusion" in _lib.last_error()
     with pytest.raises(ValueError):
         _lib.check(rc)
-    assert _lib.lib.tdssf_mlp_pack_bytes() == 2 * 133120 + 336 * 4 + 64
+    assert _lib.lib.tdssf_mlp_pack_bytes() == 2 * 139264 + 64   # two CTA images: weights 133 120 B + bias MMA operands, 1 KB-aligned
     assert _lib.lib.tdssf_cels_workspace_bytes(1000) > 1000 * 16 * 4 * 6
