@@ -28,6 +28,7 @@
 
 #include "common.cuh"
 #include "tc_ptx.cuh"
+#include "tmap.cuh"
 
 namespace tdssf {
 namespace bwd {
@@ -740,34 +741,6 @@ wgrad_reduce_kernel(const float* __restrict__ partials, int n_a, int n_cta, floa
 }  // namespace wg
 
 // ---- host side ------------------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-// cuTensorMapEncodeTiled through the runtime's driver entry point query: libtdssf.so does not link libcuda
-static EncodeTiledFn encode_tiled() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
-// bf16 row-major [rows, cols] matrix, box = [box_rows x 64 columns] (128 bytes wide), 128B swizzle, zero fill out of bounds
-static bool make_map(CUtensorMap* m, const void* base, int64_t rows, int cols, int box_rows) {
-  EncodeTiledFn enc = encode_tiled();
-  if (!enc) return false;
-  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-  const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 constexpr int kMaxW3Blocks = 1024;
 struct Work {
   uint16_t *X, *dh2, *dh1;
@@ -844,8 +817,8 @@ extern "C" int tdssf_mlp_bwd_tc(const float* x_pt, const float* x_img, const voi
     X = w.X;
   }
   CUtensorMap tm_h1_128, tm_dh1, tm_x, tm_h1, tm_dh2;
-  if (!make_map(&tm_h1_128, h1_bf16, N, kN1, 128) || !make_map(&tm_dh1, w.dh1, N, kN1, wg::kKP) || !make_map(&tm_x, X, N, kK1, wg::kKP) ||
-      !make_map(&tm_h1, h1_bf16, N, kN1, wg::kKP) || !make_map(&tm_dh2, w.dh2, N, kN2, wg::kKP)) {
+  if (!tmap::make_map(&tm_h1_128, h1_bf16, N, kN1, 128) || !tmap::make_map(&tm_dh1, w.dh1, N, kN1, wg::kKP) || !tmap::make_map(&tm_x, X, N, kK1, wg::kKP) ||
+      !tmap::make_map(&tm_h1, h1_bf16, N, kN1, wg::kKP) || !tmap::make_map(&tm_dh2, w.dh2, N, kN2, wg::kKP)) {
     set_error("tdssf_mlp_bwd_tc: cuTensorMapEncodeTiled failed (driver entry point unavailable or bad tensor geometry)");
     return TDSSF_ECUDA;
   }

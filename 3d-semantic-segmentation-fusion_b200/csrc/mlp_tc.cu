@@ -30,6 +30,7 @@
 #include <type_traits>
 #include "project.cuh"
 #include "tc_ptx.cuh"
+#include "tmap.cuh"
 
 namespace tdssf {
 namespace tc {
@@ -74,7 +75,7 @@ constexpr int kOffRing = kImageBytes;                       // 1024-aligned
 constexpr int kASlab = kTileM * 128;                        // 16 KB
 constexpr int kOffOnes = kOffRing + kStages * kASlab;       // A operand of the bias MMAs: [128 rows][16], ones in K slots 0 and 1
 constexpr int kOffBar = kOffOnes + kTileM * 32;
-constexpr int kNumBars = 2 * kStages + 2 + 6 * 2;
+constexpr int kNumBars = 3 * kStages + 2 + 6 * 2;
 constexpr int kOffTmemPtr = kOffBar + kNumBars * 8;
 constexpr int kOffGroupCtr = kOffTmemPtr + 8;              // prologue: next unclaimed group of 32 points
 constexpr int kSmemBytes = kOffTmemPtr + 16;
@@ -98,6 +99,7 @@ enum {
   kBarH1Full = kBarAcc3Full + 2,       // [2] leader: 2*kEpiWarps arrivals
   kBarH2Full = kBarH1Full + 2,         // [2]
   kBarAccFree = kBarH2Full + 2,        // [2]
+  kBarALocal = kBarAccFree + 2,        // [kStages] training only: this CTA's 8 producer warps have written the slab (TMA store of x)
 };
 
 struct Params {
@@ -541,7 +543,7 @@ __device__ __forceinline__ void project_rows(const Params& p, uint32_t cal_addr,
 // kSave: training launch, the bf16 input rows / hidden activations also go to p.x_out / p.h1_out / p.h2_out
 template <typename TokT, bool kGather, bool kSave>
 __global__ void __launch_bounds__(kThreads, 1)
-fused_mlp_kernel(const Params p) {
+fused_mlp_kernel(const Params p, const __grid_constant__ CUtensorMap tm_x) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment for the 128B-swizzled operand slabs
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -560,7 +562,8 @@ fused_mlp_kernel(const Params p) {
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(bar(kBarAFull + s), 2 * kProducerWarps);
-      ptx::mbar_init(bar(kBarAEmpty + s), 1);
+      ptx::mbar_init(bar(kBarAEmpty + s), (kSave && p.x_out != nullptr) ? 2 : 1);   // + the TMA store of the slab has read it
+      ptx::mbar_init(bar(kBarALocal + s), kProducerWarps);
     }
     ptx::mbar_init(bar(kBarWFull), 1);
     ptx::mbar_init(bar(kBarPeerW), 1);
@@ -656,18 +659,14 @@ fused_mlp_kernel(const Params p) {
           act16(va, h);
           ptx::tmem_st8(src + c * 8, h);
           if (save_h1) {
-            uint4* d = reinterpret_cast<uint4*>(p.h1_out + row * kN1 + ch * 128 + c * 16);
-            d[0] = make_uint4(h[0], h[1], h[2], h[3]);
-            d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+            ptx::stg256(p.h1_out + row * kN1 + ch * 128 + c * 16, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);   // 32 bytes per row and instruction
           }
           ptx::tmem_wait_ld();
           if (c + 2 < 8) ptx::tmem_ld16(src + (c + 2) * 16, va);
           act16(vb, h);
           ptx::tmem_st8(src + (c + 1) * 8, h);
           if (save_h1) {
-            uint4* d = reinterpret_cast<uint4*>(p.h1_out + row * kN1 + ch * 128 + (c + 1) * 16);
-            d[0] = make_uint4(h[0], h[1], h[2], h[3]);
-            d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+            ptx::stg256(p.h1_out + row * kN1 + ch * 128 + (c + 1) * 16, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);   // 32 bytes per row and instruction
           }
         }
       }
@@ -690,16 +689,12 @@ fused_mlp_kernel(const Params p) {
         act16(va, h);
         ptx::tmem_st8(dst, h);
         if (save_h2) {
-          uint4* d = reinterpret_cast<uint4*>(p.h2_out + row * kN2 + ch * 32);
-          d[0] = make_uint4(h[0], h[1], h[2], h[3]);
-          d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+          ptx::stg256(p.h2_out + row * kN2 + ch * 32, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);   // 32 bytes per row and instruction
         }
         act16(vb, h);
         ptx::tmem_st8(dst + 8, h);
         if (save_h2) {
-          uint4* d = reinterpret_cast<uint4*>(p.h2_out + row * kN2 + ch * 32 + 16);
-          d[0] = make_uint4(h[0], h[1], h[2], h[3]);
-          d[1] = make_uint4(h[4], h[5], h[6], h[7]);
+          ptx::stg256(p.h2_out + row * kN2 + ch * 32 + 16, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);   // 32 bytes per row and instruction
         }
       }
       ptx::tmem_wait_st();
@@ -827,6 +822,28 @@ fused_mlp_kernel(const Params p) {
         }
       }
       __syncwarp();
+    } else if (kSave && warp == kMmaWarp + 2) {
+      // =============================== training: x rows to HBM by TMA ================================
+      // The finished A slab IS the bf16 [128 x 64] block of x_out (128B-swizzled, which the tensor map undoes): one bulk
+      // tensor store per slab instead of 16 store instructions per producer thread in the load/store unit the gather
+      // lives on.  The slab is handed back (second arrival on its empty barrier) once the store has read it.
+      if (p.x_out != nullptr && lane == 0) {
+        uint32_t stage = 0, phase = 0;
+        for (int it = 0; it < n_iters; ++it) {
+          const int row0 = (int)tile_row0(it);
+#pragma unroll 1
+          for (int s = 0; s < kSlabs1; ++s) {
+            wait_bar(bar(kBarALocal + stage), phase, p.debug, 12);
+            ptx::tma_store_2d(&tm_x, s * kSlabK, row0, sbase + kOffRing + stage * kASlab);
+            ptx::bulk_commit_group();
+            ptx::bulk_wait_group_read<0>();
+            ptx::mbar_arrive_local(bar(kBarAEmpty + stage));
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+        ptx::bulk_wait_group<0>();
+      }
+      __syncwarp();
     }
   } else {
     // =============================== producers =====================================================
@@ -915,25 +932,18 @@ fused_mlp_kernel(const Params p) {
       constexpr int S = decltype(S_)::value;
       constexpr bool kF32 = S == 0 || kTok32;  // source elements are fp32
       float acc[8];
-      // training: the bf16 input row also goes to HBM for the weight gradient (x_out), 64 contiguous bytes per quarter-warp
-      const int64_t row = tile_row0(it) + pw * kRowsPerWarp + row_of(st, quarter);
-      uint16_t* xo = (kSave && p.x_out && row < p.N) ? p.x_out + row * kK1 + S * kSlabK : nullptr;
+      (void)it;   // (training: the finished slab goes to x_out by TMA, warp kMmaWarp + 2)
       if (kF32) {
         raw8_f32_to_f8(c.a[st], acc);
         const uint32_t w0 = pack_bf16(acc[0], acc[1]), w1 = pack_bf16(acc[2], acc[3]), w2 = pack_bf16(acc[4], acc[5]),
                        w3 = pack_bf16(acc[6], acc[7]);
         ptx::sts64(so_lo[st & 1] + slab_off + (st >> 1) * 1024, w0, w1);
         ptx::sts64(so_hi[st & 1] + slab_off + (st >> 1) * 1024, w2, w3);
-        if (xo) {
-          *reinterpret_cast<uint2*>(xo + 4 * ql) = make_uint2(w0, w1);
-          *reinterpret_cast<uint2*>(xo + 32 + 4 * ql) = make_uint2(w2, w3);
-        }
       } else {
         TokRaw<TokT>::to_f8(c.a[st], acc);
         const uint32_t w0 = pack_bf16(acc[0], acc[1]), w1 = pack_bf16(acc[2], acc[3]), w2 = pack_bf16(acc[4], acc[5]),
                        w3 = pack_bf16(acc[6], acc[7]);
         ptx::sts128(so_16[st & 1] + slab_off + (st >> 1) * 1024, w0, w1, w2, w3);
-        if (xo) *reinterpret_cast<uint4*>(xo + 8 * ql) = make_uint4(w0, w1, w2, w3);
       }
     };
     // One pipeline step: the loads of slab S2 of tile it2 go into set `nxt` (all eight of the thread at once, before
@@ -953,6 +963,7 @@ fused_mlp_kernel(const Params p) {
       __syncwarp();
       if (lane == 0) {
         ptx::mbar_arrive_cluster(leader_full0 + 8 * stage);
+        if (kSave && p.x_out != nullptr) ptx::mbar_arrive_local(bar(kBarALocal + stage));
       }
       __syncwarp();
       if (pw == 0 && it >= 4 && it < 8) TRACE(p.debug, 15, (it - 4) * 7 + S);   // slab written and announced
@@ -1041,7 +1052,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ W1, const float* _
 }
 
 template <typename TokT, bool kGather, bool kSave>
-static int launch_as(const Params& p, cudaStream_t s) {
+static int launch_as(const Params& p, const CUtensorMap& tm_x, cudaStream_t s) {
   auto kern = fused_mlp_kernel<TokT, kGather, kSave>;
   const int smem = kSmemBytes + 1024;
   static bool configured[kMaxDevices] = {};  // per instantiation and device (the attribute is per device)
@@ -1063,7 +1074,7 @@ static int launch_as(const Params& p, cudaStream_t s) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  TDSSF_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+  TDSSF_CUDA(cudaLaunchKernelEx(&cfg, kern, p, tm_x));
 #ifdef TDSSF_PROFILE
 #include "exp/mlp_tc_profile_dump.inc"
 #endif
@@ -1072,8 +1083,13 @@ static int launch_as(const Params& p, cudaStream_t s) {
 
 // the training instantiation only when something is to be saved: the inference kernel carries none of that code
 template <typename TokT, bool kGather>
-static int launch(const Params& p, cudaStream_t s) {
-  return (p.x_out || p.h1_out || p.h2_out) ? launch_as<TokT, kGather, true>(p, s) : launch_as<TokT, kGather, false>(p, s);
+static int launch(Params p, cudaStream_t s) {
+  CUtensorMap tm_x = {};   // training launches store their bf16 input rows [N, 448] with TMA out of the A ring
+  if (p.x_out && !tmap::make_map(&tm_x, p.x_out, p.N, kK1, kTileM)) {
+    set_error("tdssf_fusion_fwd: cuTensorMapEncodeTiled failed for x_bf16 (driver entry point unavailable or bad geometry)");
+    return TDSSF_ENOSUP;
+  }
+  return (p.x_out || p.h1_out || p.h2_out) ? launch_as<TokT, kGather, true>(p, tm_x, s) : launch_as<TokT, kGather, false>(p, tm_x, s);
 }
 
 __device__ __align__(16) unsigned char g_zero_rows[4096];  // zero-initialised at module load, never written
@@ -1145,8 +1161,9 @@ extern "C" int tdssf_fusion_fwd(const float* xyz, int64_t sweep_stride, int64_t 
   }
   TDSSF_REQUIRE((((uintptr_t)tokens | (uintptr_t)x_pt | (uintptr_t)logits | (uintptr_t)packed_weights) & 15) == 0 &&
                     (!rec_out || ((uintptr_t)rec_out & 15) == 0) &&
-                    (((uintptr_t)x_bf16 | (uintptr_t)h1_bf16 | (uintptr_t)h2_bf16) & 15) == 0,
+                    ((uintptr_t)x_bf16 & 15) == 0,
                 "tdssf_fusion_fwd: pointers must be 16-byte aligned");
+  TDSSF_REQUIRE((((uintptr_t)h1_bf16 | (uintptr_t)h2_bf16) & 31) == 0, "tdssf_fusion_fwd: h1_bf16 / h2_bf16 must be 32-byte aligned (256-bit stores)");
   const int64_t N = (int64_t)B * V;
   if (N == 0) return TDSSF_OK;
   if (int rc = tdssf_check_device()) return rc;
@@ -1199,6 +1216,7 @@ extern "C" int tdssf_mlp_fwd_tc(const float* x_pt, const float* x_img, int64_t N
   TDSSF_REQUIRE((((uintptr_t)x_pt | (uintptr_t)x_img | (uintptr_t)logits | (uintptr_t)packed_weights | (uintptr_t)h1_bf16 |
                   (uintptr_t)h2_bf16) & 15) == 0,
                 "tdssf_mlp_fwd_tc: pointers must be 16-byte aligned");
+  TDSSF_REQUIRE((((uintptr_t)h1_bf16 | (uintptr_t)h2_bf16) & 31) == 0, "tdssf_mlp_fwd_tc: h1_bf16 / h2_bf16 must be 32-byte aligned (256-bit stores)");
   if (N == 0) return TDSSF_OK;
   if (int rc = tdssf_check_device()) return rc;
   tc::Params p = {};

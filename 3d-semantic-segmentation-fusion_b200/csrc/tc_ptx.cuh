@@ -204,6 +204,17 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const void* tmap,
                "l"(tmap), "r"(c0), "r"(c1), "r"(bar)
                : "memory");
 }
+// 2-D tile store shared -> global (bulk async-group completion); rows / columns outside the tensor are not written
+__device__ __forceinline__ void tma_store_2d(const void* tmap, int c0, int c1, uint32_t src_smem) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(tmap), "r"(c0), "r"(c1), "r"(src_smem)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the newest kPending bulk groups of this thread have finished READING their shared-memory source
+template <int kPending>
+__device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory"); }
+template <int kPending>
+__device__ __forceinline__ void bulk_wait_group() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(kPending) : "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }

@@ -157,6 +157,7 @@ TDSSF_API int tdssf_mlp_pack_weights(const tdssf_mlp_weights* w_host, void* pack
  * x_bf16 / h1_bf16 / h2_bf16  optional (NULL to skip; training): [B*V,448] the MLP input rows [point feature | image
  *          feature] and [B*V,256] / [B*V,64] the post-ReLU activations, all in bf16 exactly as the tensor cores consumed
  *          them - what tdssf_mlp_bwd_tc needs, so that training never materialises the fp32 image feature either.
+ *          h1_bf16 / h2_bf16 32-byte aligned (256-bit stores; tdssf_mlp_bwd_tc asks the same).
  * preds_out optional [B*V] int64 class ids = argmax(logits) + 1 (first maximum, like torch.argmax; utils/losses.py:66),
  *          for the evaluation loop's confusion matrix (NULL to skip).
  * workspace: tdssf_fusion_workspace_bytes(B, V, tok_dtype) bytes, 256-byte aligned.  Holds, per point, the address of

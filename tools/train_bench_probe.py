@@ -34,3 +34,24 @@ for mode in (True, False):
     for _ in range(50): train_step(mode)
     torch.cuda.synchronize()
     print(json.dumps({"allreduce_call": mode, "step_us": (time.perf_counter() - t0) / 50 * 1e6, "graph_stats": stats()}))
+
+# host time per phase of the step (no synchronisation inside: the step is host-bound, the GPU queue stays short)
+import collections
+acc = collections.OrderedDict((k, 0.0) for k in ("zero_grads", "forward", "loss", "backward"))
+for _ in range(10): train_step(False)
+torch.cuda.synchronize()
+N_IT = 200
+for _ in range(N_IT):
+    t0 = time.perf_counter()
+    for p in params: p.grad = None
+    d_feat.grad = None
+    t1 = time.perf_counter()
+    scores = model(d_tok, d_feat, d_pts, None, st.image_sizes, st.K, st.Rt)
+    t2 = time.perf_counter()
+    total = crit(scores, d_lab, d_mask)[0]
+    t3 = time.perf_counter()
+    total.backward()
+    t4 = time.perf_counter()
+    acc["zero_grads"] += t1 - t0; acc["forward"] += t2 - t1; acc["loss"] += t3 - t2; acc["backward"] += t4 - t3
+torch.cuda.synchronize()
+print(json.dumps({"host_us_per_phase": {k: v / N_IT * 1e6 for k, v in acc.items()}}))
