@@ -265,6 +265,62 @@ def test_fused_many_sweeps_chunked(ops):
     assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
 
 
+@pytest.mark.parametrize("tok_dtype", [torch.float32, torch.bfloat16, torch.float16])
+def test_fused_saved_rows_chunked_launches(ops, tok_dtype):
+    """The training launch's saved rows (x by TMA out of the A ring, h1 / h2 from the epilogues) when the sweeps need
+    several launches (100 > 84) and the tile count is ragged, for every token type: x = bf16([x_pt | camera mean]) of the
+    stand-alone kernels (one bf16 ulp on multi-camera points), nothing outside the N rows is written."""
+    B, V = 100, 333
+    sw = synth.make_sweeps(B, V, "dinov2", seed=19, tok_dtype=tok_dtype)
+    w = synth.make_mlp_weights(19)
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    args = (sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda(), sw.encoder)
+    tok, xp = sw.tokens.cuda(), sw.point_feat.cuda()
+    N, PAD = B * V, 300
+    bufs = [torch.full((N + PAD, c), float("nan"), dtype=torch.bfloat16, device="cuda") for c in (448, 256, 64)]
+    xb, h1, h2 = (b[:N] for b in bufs)
+    logits, rec = ops.fusion_fwd(*args, tok, xp, packed, want_rec=True, save=(xb, h1, h2))
+    assert torch.equal(logits, ops.fusion_fwd(*args, tok, xp, packed))
+    for b in bufs:
+        assert torch.isnan(b[N:].float()).all() and not torch.isnan(b[:N].float()).any()
+    feat = ops.gather_mean(tok, rec)
+    want = torch.cat([xp.reshape(N, 64), feat.reshape(N, 384)], -1).bfloat16()
+    assert torch.equal(xb[:, :64], want[:, :64])
+    d = (xb.float() - want.float()).abs()
+    assert float((d / want.float().abs().clamp_min(1e-3)).max()) < 2 ** -7
+    q = lambda t: t.bfloat16().double()
+    m1 = torch.relu(xb.double() @ q(wd[0]).T + wd[1].double())
+    assert float((h1.double() - m1).abs().max() / m1.abs().max()) < 1e-2
+
+
+def test_fused_large_biases(ops):
+    """The biases enter through a K = 16 MMA as bf16 hi + lo parts: biases far larger than the products still arrive to
+    fp32 accuracy (2^-17 relative), so the logits track an fp64 model of the kernel's bf16 operand roundings."""
+    B, V = 2, 3000
+    sw = synth.make_sweeps(B, V, "dinov3", seed=23)
+    w = {k: v.clone() for k, v in synth.make_mlp_weights(23).items()}
+    gen = torch.Generator().manual_seed(23)
+    for k, scale in (("mlp.0.bias", 300.0), ("mlp.2.bias", 50.0), ("mlp.4.bias", 1000.0)):
+        w[k] = (torch.rand(w[k].shape, generator=gen) - 0.3) * scale
+    wd = [w[k].cuda() for k in W_KEYS]
+    packed = ops.pack_weights(*wd)
+    args = (sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda(), sw.encoder)
+    tok, xp = sw.tokens.cuda(), sw.point_feat.cuda()
+    logits, rec = ops.fusion_fwd(*args, tok, xp, packed, want_rec=True)
+    x = torch.cat([xp.reshape(-1, 64), ops.gather_mean(tok, rec).reshape(-1, 384)], -1)
+    q = lambda t: t.bfloat16().double()
+    h1 = torch.relu(q(x) @ q(wd[0]).T + wd[1].double())
+    h2 = torch.relu(q(h1.float()) @ q(wd[2]).T + wd[3].double())
+    ref = q(h2.float()) @ q(wd[4]).T + wd[5].double()
+    err = float((logits.reshape(-1, 16).double() - ref).abs().max() / ref.abs().max())
+    assert err < 2e-3, err
+    # and the bias alone (zero weights) is reproduced to fp32 rounding
+    zw = [torch.zeros_like(t) if i % 2 == 0 else t for i, t in enumerate(wd)]
+    only_b = ops.fusion_fwd(*args, tok, xp, ops.pack_weights(*zw)).reshape(-1, 16)
+    assert float((only_b - wd[5]).abs().max() / wd[5].abs().max()) < 1e-5
+
+
 @pytest.mark.parametrize("B,V,NC", [(1, 1, 6), (1, 255, 1), (3, 257, 3), (2, 1000, 5), (1, 40000, 6)])
 def test_fused_odd_shapes(ops, B, V, NC):
     """Tile remainders, a single point, fewer than six cameras: fused kernel against the unfused fp32 route."""
