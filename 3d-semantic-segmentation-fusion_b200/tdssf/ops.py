@@ -16,6 +16,7 @@ import torch
 from . import _lib
 from ._lib import lib, check
 
+_PACK_BYTES = lib.tdssf_mlp_pack_bytes()
 _TOK_DTYPES = {torch.float32: _lib.F32, torch.float16: _lib.F16, torch.bfloat16: _lib.BF16}
 
 
@@ -57,10 +58,13 @@ def _on_device(fn):
 # ------------------------------------------------------------------------------------------------
 # calibration stacking: mirrors multi_camera_projector's `_to_tensor` (utils/fusion_model.py:36-49)
 # ------------------------------------------------------------------------------------------------
-def stack_calibration(cam_intrinsics: Sequence, lidar2cam_extrinsics: Sequence, device) -> tuple[torch.Tensor, torch.Tensor]:
+def stack_calibration(cam_intrinsics: Sequence, lidar2cam_extrinsics: Sequence, device, image_sizes=None):
+    """(K (B,NC,3,3), Rt (B,NC,4,4)) fp32 on `device`; with `image_sizes` also hw (B,2) fp32 — host inputs go up in ONE copy."""
     n_cam = cam_intrinsics[0].shape[0]
 
     def as_f32(data):
+        if all(torch.is_tensor(item) and item.dtype == torch.float32 for item in data):
+            return list(data)
         return [torch.as_tensor(item, dtype=torch.float32) if not torch.is_tensor(item) else item.to(dtype=torch.float32)
                 for item in data]
 
@@ -69,19 +73,33 @@ def stack_calibration(cam_intrinsics: Sequence, lidar2cam_extrinsics: Sequence, 
             raise ValueError(f"Expected shape (*, {tail}) but got {tuple(t.shape)}.")
 
     ks, rts = as_f32(cam_intrinsics), as_f32(lidar2cam_extrinsics)
-    if all(not t.is_cuda for t in ks) and all(not t.is_cuda for t in rts):
-        # the loops hand over lists of host tensors (utils/train.py:83): one stack and ONE upload for both
+    hw = None
+    if not any(t.is_cuda for t in ks) and not any(t.is_cuda for t in rts):
+        # the loops hand over lists of host tensors (utils/train.py:83): one stack and ONE upload for everything
         K, Rt = torch.stack(ks, dim=0), torch.stack(rts, dim=0)
         check(K, (n_cam, 3, 3))
         check(Rt, (n_cam, 4, 4))
         B = K.shape[0]
-        flat = torch.cat([K.reshape(-1), Rt.reshape(-1)]).to(device, non_blocking=True)
-        return flat[:K.numel()].view(B, n_cam, 3, 3), flat[K.numel():].view(B, n_cam, 4, 4)   # contiguous views of one buffer
-    K = torch.stack([t.to(device) for t in ks], dim=0)
-    Rt = torch.stack([t.to(device) for t in rts], dim=0)
-    check(K, (n_cam, 3, 3))
-    check(Rt, (n_cam, 4, 4))
-    return K.contiguous(), Rt.contiguous()
+        parts = [K.reshape(-1), Rt.reshape(-1)]
+        hw_host = image_sizes is not None and not (torch.is_tensor(image_sizes) and image_sizes.is_cuda)
+        if hw_host:
+            h = torch.as_tensor(image_sizes, dtype=torch.float32)
+            if tuple(h.shape) != (B, 2):
+                raise ValueError("image_sizes must be of shape (B, 2) where each entry is (H, W).")
+            parts.append(h.reshape(-1))
+        flat = torch.cat(parts).to(device, non_blocking=True)
+        nk, nr = K.numel(), Rt.numel()
+        K, Rt = flat[:nk].view(B, n_cam, 3, 3), flat[nk:nk + nr].view(B, n_cam, 4, 4)   # contiguous views of one buffer
+        if hw_host:
+            hw = flat[nk + nr:].view(B, 2)
+    else:
+        K = torch.stack([t.to(device) for t in ks], dim=0).contiguous()
+        Rt = torch.stack([t.to(device) for t in rts], dim=0).contiguous()
+        check(K, (n_cam, 3, 3))
+        check(Rt, (n_cam, 4, 4))
+    if image_sizes is None:
+        return K, Rt
+    return K, Rt, (hw if hw is not None else image_sizes_f32(image_sizes, K.shape[0], device))
 
 
 def image_sizes_f32(image_sizes, B: int, device) -> torch.Tensor:
@@ -176,14 +194,13 @@ def _weights_struct(params: Sequence[torch.Tensor]) -> _lib.MlpWeights:
 
 def _flat_zero_grads(params: Sequence[torch.Tensor]) -> list:
     """The six parameter gradients as views of ONE zero-filled fp32 buffer (one fill launch instead of six; the bias
-    sums are accumulated with atomics, so they start from zero).  Every view starts on a 16-byte boundary."""
+    sums are accumulated, so they start from zero).  Every view starts on a 16-byte boundary: the reference shapes
+    (checked by _weights_struct) all have a multiple of four elements."""
     sizes = [t.numel() for t in params]
-    flat = torch.zeros(sum((n + 3) & ~3 for n in sizes), dtype=torch.float32, device=params[0].device)
-    out, off = [], 0
-    for t, n in zip(params, sizes):
-        out.append(flat[off:off + n].view(t.shape))
-        off += (n + 3) & ~3
-    return out
+    if any(n & 3 for n in sizes):
+        raise ValueError("parameter sizes must be multiples of 4 elements")
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device=params[0].device)
+    return [piece.view(t.shape) for piece, t in zip(flat.split_with_sizes(sizes), params)]
 
 
 class _MlpF32(torch.autograd.Function):
@@ -234,8 +251,9 @@ def mlp_f32(x_pt, x_img, W1, b1, W2, b2, W3, b3):
 def pack_weights(W1, b1, W2, b2, W3, b3) -> torch.Tensor:
     """bf16 tensor-core operand image of the MLP weights (both CTA ranks + biases)."""
     _need_cuda(W1)
-    params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
-    packed = torch.empty(lib.tdssf_mlp_pack_bytes(), dtype=torch.uint8, device=W1.device)
+    params = [t if (not t.requires_grad and t.dtype == torch.float32 and t.is_contiguous()) else _f32c(t.detach())
+              for t in (W1, b1, W2, b2, W3, b3)]
+    packed = torch.empty(_PACK_BYTES, dtype=torch.uint8, device=W1.device)
     ws = _weights_struct(params)
     check(lib.tdssf_mlp_pack_weights(C.byref(ws), _ptr(packed), _stream(W1)), "tdssf_mlp_pack_weights")
     return packed
@@ -361,8 +379,7 @@ class _FusedTrain(torch.autograd.Function):
     @_on_device
     def forward(ctx, x_pt, W1, b1, W2, b2, W3, b3, points, K, Rt, img_hw, encoder, tokens):
         params = [_f32c(t.detach()) for t in (W1, b1, W2, b2, W3, b3)]
-        _weights_struct(params)  # shape check
-        packed = pack_weights(*params)
+        packed = pack_weights(*params)   # (checks the shapes)
         B, V = x_pt.shape[0], x_pt.shape[1]
         N = B * V
         dev = x_pt.device

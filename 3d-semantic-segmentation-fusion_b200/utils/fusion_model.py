@@ -109,8 +109,7 @@ class FeatureFusionModel(nn.Module):
 
         device = _device_of(voxel_raw, self.device)
         enc = self.image_encoder
-        K, Rt = ops.stack_calibration(cam_intrinsics, lidar2cam_extrinsics, device)
-        hw = ops.image_sizes_f32(image_sizes, B, device)
+        K, Rt, hw = ops.stack_calibration(cam_intrinsics, lidar2cam_extrinsics, device, image_sizes)
         tokens = patch_tokens.to(device, non_blocking=True)  # the reference moves them per camera (F11)
         voxel_raw = voxel_raw.to(device)
         voxel_features = voxel_features.to(device)

@@ -55,3 +55,26 @@ for _ in range(N_IT):
     acc["zero_grads"] += t1 - t0; acc["forward"] += t2 - t1; acc["loss"] += t3 - t2; acc["backward"] += t4 - t3
 torch.cuda.synchronize()
 print(json.dumps({"host_us_per_phase": {k: v / N_IT * 1e6 for k, v in acc.items()}}))
+
+# finer: wall time inside selected host functions (wrappers add ~0.3 us per call)
+from tdssf import ops as _ops
+import utils.fusion_model as _fm
+tacc = collections.OrderedDict()
+def wrap(obj, name, label=None):
+    fn = getattr(obj, name); label = label or name
+    tacc[label] = 0.0
+    def timed(*a, **k):
+        t = time.perf_counter()
+        try: return fn(*a, **k)
+        finally: tacc[label] += time.perf_counter() - t
+    setattr(obj, name, timed)
+for n in ("stack_calibration", "image_sizes_f32", "pack_weights", "fusion_fwd", "_flat_zero_grads", "_fusion_workspace", "_weights_struct"):
+    wrap(_ops, n)
+for n in ("tdssf_fusion_fwd", "tdssf_mlp_pack_weights", "tdssf_mlp_bwd_tc", "tdssf_cels_count", "tdssf_cels_fwd_bwd_counted"):
+    wrap(_ops.lib, n, "C:" + n)
+for _ in range(5): train_step(False)
+for k in tacc: tacc[k] = 0.0
+torch.cuda.synchronize()
+for _ in range(N_IT): train_step(False)
+torch.cuda.synchronize()
+print(json.dumps({"host_us_inside": {k: round(v / N_IT * 1e6, 1) for k, v in tacc.items()}}))
