@@ -11,11 +11,13 @@
 //                pointer per point into the workspace (token row / zero row / scratch row holding the camera mean of
 //                a multi-camera point), camera records to rec_out.  Done up front because once the gather saturates
 //                the load/store unit every memory instruction of another warp queues for hundreds of cycles.
-//   warps 0-7    epilogue (72 regs): TMEM -> registers -> bias/ReLU -> bf16 -> TMEM (A operand of the next layer), in
+//   warps 0-7    epilogue (72 regs): TMEM -> registers -> ReLU -> bf16 -> TMEM (A operand of the next layer; the biases are
+//                already in the accumulators: one ones x bias MMA per layer), in
 //                16-column chunks with the next TMEM load in flight; last layer -> logits to HBM
 //   warp  8      TMEM allocation, weight load (cp.async.bulk), layer-1 MMA issue (leader CTA only)       (64 regs)
 //   warp  9      layer-2 / layer-3 MMA issue as soon as the epilogue has written H1 / H2 (leader CTA only)
-//   warps 10-11  idle after the prologue (keep the warpgroups aligned; their registers go to the producers)
+//   warps 10-11  idle after the prologue (keep the warpgroups aligned; their registers go to the producers); in training
+//                launches one thread of warp 10 stores every finished A slab to x_bf16 (TMA tensor store)
 //   warps 12-19  producers (136 regs): per 64-channel K slab, gather of the rows' sources (L2/HBM) with
 //                [pointer + immediate] loads, fp32 -> bf16, written in the 128B-swizzled K-major layout the UMMA
 //                descriptor expects.  A thread owns a quarter of four rows; three register sets: the loads of slabs
