@@ -194,7 +194,7 @@ emit("config3", "training step per GPU, TDSSF_MLP=fp32 (drop-in modules: forward
      note="4 sweeps x 34 720 points; project + gather + fp32 MLP fwd, cels fwd/bwd, fp32 MLP bwd; no optimizer, no all-reduce")
 os.environ["TDSSF_MLP"] = "bf16"
 ms = timeit(train_step, n=5)
-emit("config3", "training step per GPU, default bf16 (fused tcgen05 forward, bf16 backward with cuBLAS GEMMs)", ms, Bt * V, "points",
+emit("config3", "training step per GPU, default bf16 (fused tcgen05 forward, tcgen05 backward: data-gradient chain + weight-gradient kernels)", ms, Bt * V, "points",
      note="4 sweeps x 34 720 points; fused launch saving its bf16 input rows + activations, cels fwd/bwd, bf16 backward")
 wt = [t.clone().requires_grad_(True) for t in wd]
 featt = feat.clone().requires_grad_(True)
@@ -210,7 +210,7 @@ def mlp_tc_train_step():
 
 ms = timeit(mlp_tc_train_step, n=5)
 emit("a6", "mlp_fwd_tc (saving h1/h2) + mlp_bwd_tc", ms, N, "points", flops_per_unit=3 * flops - 2 * 384 * 256,
-     note="8 sweeps; bf16 tensor-core forward + bf16 backward (cuBLAS GEMMs, own element-wise kernels); frac is against the fp32 FMA peak for comparison with the fp32 row")
+     note="8 sweeps; bf16 tensor-core forward + tcgen05 backward (hand-written chain + weight-gradient kernels); frac is against the fp32 FMA peak for comparison with the fp32 row")
 
 
 def fused_train_step():
