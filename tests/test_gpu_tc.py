@@ -338,6 +338,32 @@ def test_fused_odd_shapes(ops, B, V, NC):
     assert _rel(logits.cpu().numpy(), ref.cpu().numpy()) < BF16_TOL
 
 
+def test_fused_forward_under_cuda_graph_capture(ops):
+    """After one warm-up call (workspace allocated, kernel attributes set) the fused launch is a pure stream operation:
+    it can be captured into a CUDA graph and replayed - new point features in the same buffers give the eager result."""
+    sw = synth.make_sweeps(2, 6000, "dinov3", seed=77)
+    w = synth.make_mlp_weights(77)
+    packed = ops.pack_weights(*[w[k].cuda() for k in W_KEYS])
+    args = (sw.points.cuda(), torch.stack(sw.K).cuda(), torch.stack(sw.Rt).cuda(), sw.image_sizes.float().cuda(), sw.encoder)
+    tok, xp = sw.tokens.cuda(), sw.point_feat.cuda().clone()
+    out = torch.empty(2, 6000, 16, device="cuda")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        ops.fusion_fwd(*args, tok, xp, packed, out=out)          # warm-up on the capture stream (its workspace)
+        side.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            ops.fusion_fwd(*args, tok, xp, packed, out=out)
+    torch.cuda.current_stream().wait_stream(side)
+    xp.copy_(torch.randn(xp.shape, generator=torch.Generator().manual_seed(78)).cuda())
+    out.fill_(float("nan"))
+    g.replay()
+    torch.cuda.synchronize()
+    want = ops.fusion_fwd(*args, tok, xp, packed)
+    assert torch.equal(out, want)
+
+
 def test_fused_preds_out(ops):
     """The class ids written by the fused launch are torch.argmax(logits) + 1 of the logits it wrote (utils/losses.py:66)."""
     sw = synth.make_sweeps(2, 5000, "dinov3", seed=21)
