@@ -63,6 +63,12 @@ SIGNATURES = {
     "tdssf_cels_graph_stats": (None, [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "tdssf_cels_backward": (_i, [_p, _sz, _i64, _i64, _p, _p, _p, _p]),
     "tdssf_confusion": (_i, [_p, _p, _i64, _i, _p, _p]),
+    "tdssf_p2p_buffer_bytes": (_sz, [_i64]),
+    "tdssf_p2p_create": (_i, [_i64, C.POINTER(C.c_void_p), _p]),
+    "tdssf_p2p_open": (_i, [_p, C.POINTER(C.c_void_p)]),
+    "tdssf_p2p_close": (_i, [_p]),
+    "tdssf_p2p_destroy": (_i, [_p]),
+    "tdssf_p2p_allreduce_mean": (_i, [C.POINTER(C.c_void_p), _i, _i, _p, _i64, _i64, C.c_uint32, _p]),
     "tdssf_compose_lidar2cam": (_i, [_p, _p, _p, _p, _i, _i, _p, _p, _p]),
     "tdssf_compose_sweep2ref": (_i, [_p, _p, _p, _p, _i, _p, _p]),
     "tdssf_accumulate_sweeps": (_i, [_p, _i64, _p, _p, _i, _i, _p, _p, _p]),

@@ -57,6 +57,71 @@ def allreduce_confusion(cm: torch.Tensor) -> torch.Tensor:
     return cm
 
 
+class _PeerExchange:
+    """NVLink peer-memory exchange of one process group (tdssf_p2p_*): every rank's buffer mapped into every process.
+    Set up once, collectively; `ok` is the group's common verdict (any failure anywhere -> everybody uses NCCL)."""
+
+    def __init__(self, max_floats: int, device: torch.device):
+        import ctypes as C
+        from ._lib import lib
+        self.lib, self.C = lib, C
+        self.rank, self.world = world()
+        self.max_floats = int(max_floats)
+        self.device = device
+        self.epoch = 0
+        self.own = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        good = 1
+        with torch.cuda.device(device):
+            if self.world > 16 or lib.tdssf_p2p_create(self.max_floats, C.byref(self.own), handle) != 0:
+                good = 0
+        mine = torch.tensor(list(bytes(handle)) + [good], dtype=torch.uint8, device=device)
+        everyone = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(everyone, mine)
+        rows = [bytes(t.cpu().tolist()) for t in everyone]
+        good = int(all(r[64] == 1 for r in rows))
+        self.bufs = (C.c_void_p * self.world)()
+        if good:
+            with torch.cuda.device(device):
+                for r, row in enumerate(rows):
+                    if r == self.rank:
+                        self.bufs[r] = self.own.value
+                        continue
+                    peer = C.c_void_p()
+                    h = (C.c_ubyte * 64).from_buffer_copy(row[:64])
+                    if lib.tdssf_p2p_open(h, C.byref(peer)) != 0:
+                        good = 0
+                        break
+                    self.bufs[r] = peer.value
+        verdict = torch.tensor([good], dtype=torch.int32, device=device)
+        dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
+        self.ok = bool(int(verdict.item()))
+
+    def allreduce_mean(self, flat: torch.Tensor) -> None:
+        from ._lib import check
+        self.epoch += 1
+        with torch.cuda.device(self.device):
+            stream = self.C.c_void_p(torch._C._cuda_getCurrentRawStream(self.device.index))
+            check(self.lib.tdssf_p2p_allreduce_mean(self.bufs, self.world, self.rank, self.C.c_void_p(flat.data_ptr()), flat.numel(),
+                                                    self.max_floats, self.epoch & 0xffffffff or 1, stream), "tdssf_p2p_allreduce_mean")
+
+
+_peer_exchange: dict = {}   # (device index, bucket size) -> _PeerExchange of the default group
+
+
+def _peers_for(n_floats: int, device: torch.device):
+    """The default group's peer exchange for a bucket of n_floats, or None (NCCL) - decided collectively, once per size:
+    NCCL backend, one node, TDSSF_P2P != 0, every rank's set-up succeeded."""
+    import os
+    if os.environ.get("TDSSF_P2P", "1") == "0" or dist.get_backend() != "nccl" or n_floats % 4 or n_floats == 0:
+        return None
+    key = (device.index, n_floats)
+    if key not in _peer_exchange:
+        _peer_exchange[key] = _PeerExchange(n_floats, device)
+    ex = _peer_exchange[key]
+    return ex if ex.ok else None
+
+
 def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
     """Average the gradients of `params` over ranks through one flat fp32 bucket; parameters without a gradient on
     this rank contribute zeros (a rank whose sweeps had no valid labels).  Returns the bucket's element count."""
@@ -67,24 +132,35 @@ def allreduce_mean_grads(params: Iterable[torch.nn.Parameter]) -> int:
     if w == 1:
         return sum(p.numel() for p in params)   # nothing to average
     dev = params[0].device
+    total = sum(p.numel() for p in params)
+    # CUDA ranks of one node: ONE kernel over NVLink peer memory (csrc/p2p.cu) instead of a library collective; the choice
+    # depends only on the group and the bucket size, so every rank takes the same branch whatever its gradients look like
+    peers = _peers_for(total, dev) if dev.type == "cuda" else None
     shared = _shared_flat_grad(params)
-    if shared is not None:
+    if shared is not None and shared.numel() == total:
         # the bf16 backward hands out the six gradients as views of one buffer (tdssf.ops._flat_zero_grads) and autograd
         # keeps them: the bucket already exists, reduce it in place (one collective, no gather / scatter copies)
-        if w > 1:
-            if dist.get_backend() == "nccl":
-                dist.all_reduce(shared, op=dist.ReduceOp.AVG)
-            else:
-                dist.all_reduce(shared, op=dist.ReduceOp.SUM)
-                shared.div_(w)
+        if peers is not None and shared.data_ptr() % 16 == 0:
+            peers.allreduce_mean(shared)
+        elif peers is not None:
+            tmp = shared.clone()
+            peers.allreduce_mean(tmp)
+            shared.copy_(tmp)
+        elif dist.get_backend() == "nccl":
+            dist.all_reduce(shared, op=dist.ReduceOp.AVG)
+        else:
+            dist.all_reduce(shared, op=dist.ReduceOp.SUM)
+            shared.div_(w)
         return shared.numel()
-    flat = torch.zeros(sum(p.numel() for p in params), dtype=torch.float32, device=dev)
+    flat = torch.zeros(total, dtype=torch.float32, device=dev)
     off = 0
     for p in params:
         if p.grad is not None:
             flat[off:off + p.numel()].copy_(p.grad.reshape(-1))
         off += p.numel()
-    if w > 1:
+    if peers is not None:
+        peers.allreduce_mean(flat)
+    else:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM)
         flat.div_(w)
     off = 0

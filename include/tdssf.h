@@ -324,6 +324,26 @@ TDSSF_API int tdssf_compose_sweep2ref(const double* sweep_sensor, const double* 
 TDSSF_API int tdssf_accumulate_sweeps(const float* pts, int64_t sweep_stride_floats, const int32_t* counts, const double* T_f64,
                                       int S, int P, float* out, int32_t* out_total, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Multi-GPU: mean all-reduce of the fusion-MLP gradient bucket over NVLink peer memory - one kernel per step
+ * in place of a library collective (the reference is single-process: no counterpart; semantics per SURVEY 8e: sum over
+ * ranks / world size).  One process per GPU on ONE node; every rank creates an exchange buffer, the 64-byte handles are
+ * exchanged by the host side (torch.distributed in tdssf/parallel.py) and opened by the peers.
+ *   tdssf_p2p_create / _open / _close / _destroy   one-time set-up and tear-down (create allocates and synchronises)
+ *   tdssf_p2p_allreduce_mean   grad[0..n_floats) := mean over ranks, in place, ONE launch on `stream`, no allocation, no host
+ *                              synchronisation.  bufs_host: `world` pointers, this process's mappings of every rank's buffer
+ *                              (its own at index `rank`).  epoch: the group's call count from 1, identical on all ranks.
+ *                              n_floats % 4 == 0, n_floats <= max_floats, grad 16-byte aligned, world <= 16.
+ *                              Every rank must call it the same number of times; the sum is formed in rank order on every
+ *                              rank (bit-identical results across ranks). */
+TDSSF_API size_t tdssf_p2p_buffer_bytes(int64_t max_floats);
+TDSSF_API int tdssf_p2p_create(int64_t max_floats, void** buf_out, void* handle_out_host /* 64 bytes */);
+TDSSF_API int tdssf_p2p_open(const void* handle_host /* 64 bytes */, void** peer_buf_out);
+TDSSF_API int tdssf_p2p_close(void* peer_buf);
+TDSSF_API int tdssf_p2p_destroy(void* own_buf);
+TDSSF_API int tdssf_p2p_allreduce_mean(void* const* bufs_host, int world, int rank, float* grad, int64_t n_floats, int64_t max_floats,
+                                       uint32_t epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -56,8 +56,28 @@ cm = ops.confusion(preds, gt, 16)
 parallel.allreduce_confusion(cm)
 torch.cuda.synchronize()
 
+# the gradient bucket over NVLink peer memory (csrc/p2p.cu) against NCCL: 40 consecutive calls (epoch / parity protocol)
+p2p = {"grad_allreduce": "nccl" if world > 1 else "none"}
+if world > 1:
+    n_bucket = sum(p.numel() for p in params)
+    ex = parallel._peers_for(n_bucket, dev)
+    if ex is not None:
+        gen = torch.Generator().manual_seed(100 + rank)
+        worst, same = 0.0, True
+        for it in range(40):
+            x = torch.randn(n_bucket, generator=gen).to(dev)
+            want = x.clone()
+            dist.all_reduce(want, op=dist.ReduceOp.AVG)
+            ex.allreduce_mean(x)
+            worst = max(worst, float((x - want).abs().max()))
+            lo, hi = x.double().sum().reshape(1).clone(), x.double().sum().reshape(1).clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            same = same and bool((lo == hi).item())
+        p2p = {"grad_allreduce": "p2p", "p2p_vs_nccl_max_abs": worst, "p2p_identical_across_ranks": same}
+
 ok = True
-out = {"world": world}
+out = {"world": world, **p2p}
 if rank == 0:
     acc, cm_want, losses = None, np.zeros((16, 16), np.int64), []
     for r in range(world):
@@ -79,6 +99,8 @@ if rank == 0:
     out.update(grad_rel_err_vs_mean_of_oracle_shards=errs, loss_rank0=float(total), loss_oracle_rank0=losses[0],
                confusion_equals_oracle_union=same, confusion_total=int(cm.sum()))
     ok = max(errs.values()) < 1e-5 * 20 and same and abs(float(total) - losses[0]) < 1e-5 * abs(losses[0])
+    if p2p["grad_allreduce"] == "p2p":
+        ok = ok and p2p["p2p_vs_nccl_max_abs"] < 1e-5 and p2p["p2p_identical_across_ranks"]
     out["ok"] = ok
     print(json.dumps(out), flush=True)
 if world > 1:
