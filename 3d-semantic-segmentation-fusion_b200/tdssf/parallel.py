@@ -9,7 +9,11 @@ cross ranks, both outside the kernels and both tiny:
     * the fusion-MLP gradients of one training step (132 k fp32 parameters, mlp.{0,2,4}) — averaged, in ONE flat
       bucket (0.5 MB: launch-latency bound on NVSwitch, so one collective, not six).
 
-`torch.distributed` is the plumbing (NCCL on the GPUs, gloo in the CPU tests); nothing here touches the kernels.
+`torch.distributed` is the plumbing (NCCL on the GPUs, gloo in the CPU tests).  The gradient bucket of CUDA ranks that
+share a node does not go through NCCL: csrc/p2p.cu averages it with ONE kernel over NVLink peer memory (every rank's
+exchange buffer mapped into every process through CUDA IPC, set up collectively at the first call; any failure anywhere,
+several nodes, another backend or TDSSF_P2P=0 -> everybody uses ncclAllReduce).  At 0.5 MB the collective is launch-
+latency bound: the kernel costs one launch from a ctypes call where the ProcessGroup route costs ~70 us of host time.
 """
 from __future__ import annotations
 

@@ -16,7 +16,8 @@ Sub-records of the same JSON line (each with its own timing, launches per step a
   tok16      the same batch with bf16 patch tokens (SURVEY f2 hand-off, 712.9 algorithmic B/pt)
   config4    BASELINE configs[3]: one 350 000-point cloud, 56x100 token maps (tensor-bound regime)
   train      BASELINE configs[2]: 4 sweeps per rank, fused forward saving its bf16 rows -> CE + Lovasz-Softmax -> backward ->
-             ONE all-reduce (mean) of the 132 432 MLP gradients over NCCL when N > 1
+             ONE mean all-reduce of the 132 432 MLP gradients when N > 1 (a tdssf kernel over NVLink peer memory; NCCL when the
+             peer set-up is not possible)
   eval       BASELINE configs[4]: per-rank shard of sweeps, fused forward writing class ids -> int64 confusion matrix on
              the device, ONE int64 all-reduce at the end, mIoU
 
@@ -578,12 +579,16 @@ def sub_records(args, rank, world, dev, timer, peaks, peak_kind, sw, wd, packed,
     from tdssf import _lib
     gs = [C.c_int64(), C.c_int64(), C.c_int64()]
     _lib.lib.tdssf_cels_graph_stats(*[C.byref(g) for g in gs])
+    grad_path = "none"
+    if world > 1:   # which branch tdssf.parallel.allreduce_mean_grads took for this bucket (decided collectively at its first call)
+        ex = parallel._peer_exchange.get((dev.index, sum(p.numel() for p in params)))
+        grad_path = "one tdssf kernel over NVLink peer memory, csrc/p2p.cu" if ex is not None and ex.ok else "ncclAllReduce"
     tf = FLOPS_TRAIN * PER * V / (step_ms * 1e-3) / 1e12
     out["train"] = {
         "workload": f"BASELINE configs[2]: {PER} sweeps x {V} pts per GPU, fused forward (saving bf16 rows) + CE/Lovasz-Softmax + backward"
-                    + (f" + all-reduce(mean) of the 132432 MLP gradients over NCCL x{world}" if world > 1 else " (no all-reduce at N=1)"),
+                    + (f" + all-reduce(mean) of the 132432 MLP gradients x{world} ({grad_path})" if world > 1 else " (no all-reduce at N=1)"),
         "value": world * PER * V / (step_ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": step_ms,
-        "loss": float(loss.detach()), "launches": counts,
+        "loss": float(loss.detach()), "launches": counts, "grad_allreduce": grad_path,
         "cels_graph": {"replays": gs[0].value, "captures": gs[1].value, "plain_sequences": gs[2].value},
         "roofline": {"bound": "tensor", "achieved": tf, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": tf / peaks["bf16_tflops"],
                      "flops_per_point": FLOPS_TRAIN,
