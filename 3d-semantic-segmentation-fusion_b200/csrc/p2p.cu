@@ -59,7 +59,7 @@ allreduce_mean_kernel(const Peers peers, int world, int rank, float* __restrict_
     const uint32_t* f = reinterpret_cast<const uint32_t*>(own) + ((size_t)parity * kMaxRanks + threadIdx.x) * kMaxChunks + j;
     const long long t0 = clock64();
     while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
-      if (clock64() - t0 > 20000000000LL) {   // ~10 s: a rank never launched its side
+      if (clock64() - t0 > 240000000000LL) {   // ~2 min: a rank never launched its side (ranks may be seconds apart: data loading)
         if (debug) atomicExch(debug, 31u | 0x80000000u);
         __trap();
       }
